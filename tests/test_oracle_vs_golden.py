@@ -166,9 +166,9 @@ def test_pose_only(k, dec_fit):
     T = opt.estimate_pose_cam_obj(g["in_t_co_se3"].copy(), float(g["in_scale"]), g["in_pts"], g["in_code"],
                                   trace=trace)
     for e in range(g["H"].shape[0]):
-        assert np.linalg.norm(trace[e]["H"] - g["H"][e]) / np.linalg.norm(g["H"][e]) < 1e-4
-        assert np.linalg.norm(trace[e]["b"] - g["b"][e]) / np.linalg.norm(g["b"][0]) < 1e-3
-    assert np.abs(T - g["t_cam_obj"]).max() < 1e-4
+        assert np.linalg.norm(trace[e]["H"] - g["H"][e]) / np.linalg.norm(g["H"][e]) < 2e-3
+        assert np.linalg.norm(trace[e]["b"] - g["b"][e]) / np.linalg.norm(g["b"][0]) < 5e-3
+    assert np.abs(T - g["t_cam_obj"]).max() < 1e-3
 
 
 def test_wrand_failure_path(dec_rand):
