@@ -1,0 +1,423 @@
+// C ABI of libdspslam_sm100 (include/dspslam.h): handle, weight packing, workspace,
+// and the launch sequences of the Gauss-Newton drivers.  No exception crosses the ABI.
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/dspslam.h"
+#include "kernels.h"
+#include "kernels_tc.h"
+
+using namespace dsp;
+
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess)                                                                    \
+            return fail(DSPSLAM_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));       \
+    } while (0)
+
+struct dspslam_handle {
+    int device = 0;
+    int sm_count = 0;
+    DecoderDev dec{};
+    float* wblob = nullptr;      // FP32 packed parameters
+    __half* hblob = nullptr;     // FP16 tcgen05 operand tiles
+    char* ws = nullptr;          // scratch, grown on demand
+    size_t ws_cap = 0;
+    float* lat = nullptr;        // c0 | c4 of the single-code entry points (2 x 512) + staging
+    int32_t* zeros = nullptr;    // zero offsets for the ray-less pose-only driver
+    size_t zeros_cap = 0;
+    int64_t launches = 0;
+    bool tc_ready = false;
+    std::mutex mu;
+};
+
+namespace {
+
+struct Carver {   // bump allocator over the workspace (256-byte aligned pieces)
+    size_t off = 0;
+    size_t take(size_t bytes) {
+        size_t at = off;
+        off += (bytes + 255) & ~(size_t)255;
+        return at;
+    }
+};
+
+int ensure_ws(dspslam_handle* h, size_t bytes) {
+    if (bytes <= h->ws_cap) return 0;
+    if (h->ws) {
+        CK(cudaDeviceSynchronize());
+        CK(cudaFree(h->ws));
+        h->ws = nullptr;
+        h->ws_cap = 0;
+    }
+    size_t want = bytes + bytes / 8;
+    cudaError_t e = cudaMalloc(&h->ws, want);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        e = cudaMalloc(&h->ws, bytes);
+        want = bytes;
+    }
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        char buf[128];
+        snprintf(buf, sizeof buf, "workspace allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+        return fail(DSPSLAM_E_NOMEM, buf);
+    }
+    h->ws_cap = want;
+    return 0;
+}
+
+// ---- FP32 parameter packing ----------------------------------------------------------------
+struct Packer {
+    std::vector<float> buf;
+    size_t add(size_t n) {            // 64-float aligned, zero-filled
+        size_t at = (buf.size() + 63) & ~(size_t)63;
+        buf.resize(at + n, 0.f);
+        return at;
+    }
+};
+
+int pack_fp32(dspslam_handle* h, const float* const* W, const float* const* b) {
+    DecoderDev& d = h->dec;
+    const int L = d.L, in_dim = d.in_dim, h3 = d.h3, h3p = d.h3p;
+    Packer P;
+    size_t oWt0 = P.add((size_t)in_dim * HID);
+    for (int i = 0; i < in_dim; ++i)
+        for (int o = 0; o < HID; ++o) P.buf[oWt0 + (size_t)i * HID + o] = W[0][(size_t)o * in_dim + i];
+    size_t oW0x4 = P.add(4 * HID);
+    for (int a = 0; a < 3; ++a)
+        for (int o = 0; o < HID; ++o) P.buf[oW0x4 + (size_t)a * HID + o] = W[0][(size_t)o * in_dim + L + a];
+    size_t oWt[8] = {0}, oWn[8] = {0}, oB[8] = {0};
+    for (int k = 1; k < 8; ++k) {
+        const int K = (k == 4) ? h3p : HID;                 // padded reduction size of the forward product
+        const int N = (k == 3) ? h3p : HID;                 // padded output size
+        const int Kreal = (k == 4) ? h3 : HID, Nreal = (k == 3) ? h3 : HID;
+        const int ld_in = HID;                              // W[k] is [Nreal][512]
+        oWt[k] = P.add((size_t)K * N);
+        for (int kk = 0; kk < Kreal; ++kk)
+            for (int n = 0; n < Nreal; ++n) P.buf[oWt[k] + (size_t)kk * N + n] = W[k][(size_t)n * ld_in + kk];
+        // natural copy for the backward sweep: rows = outputs (padded for k==3), 512 columns
+        const int R = (k == 3) ? h3p : HID;
+        oWn[k] = P.add((size_t)R * HID);
+        for (int o = 0; o < Nreal; ++o)
+            memcpy(&P.buf[oWn[k] + (size_t)o * HID], &W[k][(size_t)o * ld_in], sizeof(float) * HID);
+    }
+    size_t oW4in = P.add((size_t)in_dim * HID);
+    for (int i = 0; i < in_dim; ++i)
+        for (int n = 0; n < HID; ++n) P.buf[oW4in + (size_t)i * HID + n] = W[4][(size_t)n * HID + h3 + i];
+    for (int k = 0; k < 8; ++k) {
+        const int Nreal = (k == 3) ? h3 : HID;
+        oB[k] = P.add(HID);
+        memcpy(&P.buf[oB[k]], b[k], sizeof(float) * Nreal);
+    }
+    size_t ow8 = P.add(HID);
+    memcpy(&P.buf[ow8], W[8], sizeof(float) * HID);
+    d.b8 = b[8][0];
+
+    CK(cudaMalloc(&h->wblob, P.buf.size() * sizeof(float)));
+    CK(cudaMemcpy(h->wblob, P.buf.data(), P.buf.size() * sizeof(float), cudaMemcpyHostToDevice));
+    const float* base = h->wblob;
+    d.Wt0 = base + oWt0;
+    d.W0x4 = base + oW0x4;
+    d.W4in = base + oW4in;
+    d.w8 = base + ow8;
+    d.Wt[0] = nullptr;
+    d.Wn[0] = nullptr;
+    for (int k = 1; k < 8; ++k) { d.Wt[k] = base + oWt[k]; d.Wn[k] = base + oWn[k]; }
+    for (int k = 0; k < 8; ++k) d.bias[k] = base + oB[k];
+    return 0;
+}
+
+inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+int check_launch(dspslam_handle* h, int n_launch, const char* what) {
+    h->launches += n_launch;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(DSPSLAM_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return 0;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace
+
+extern "C" {
+
+int dspslam_abi_version(void) { return DSPSLAM_ABI_VERSION; }
+const char* dspslam_last_error(void) { return g_err.c_str(); }
+int64_t dspslam_launch_count(const dspslam_handle* h) { return h ? h->launches : 0; }
+
+int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host, const float* const* b_host,
+                   int device, dspslam_handle** out) {
+    if (!desc || !W_host || !b_host || !out) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (desc->hidden != HID || desc->n_hidden != 8 || desc->latent_in != 4 || desc->code_len < 1 ||
+        desc->code_len > MAX_L)
+        return fail(DSPSLAM_E_UNSUPPORTED,
+                    "supported decoder family: 8 hidden layers of 512, latent_in=[4], code_len 1..64");
+    int ndev = 0;
+    CK(cudaGetDeviceCount(&ndev));
+    if (device < 0 || device >= ndev) return fail(DSPSLAM_E_BADARG, "bad device index");
+    dspslam_handle* h = new (std::nothrow) dspslam_handle();
+    if (!h) return fail(DSPSLAM_E_NOMEM, "host allocation failed");
+    h->device = device;
+    DeviceGuard g(device);
+    cudaDeviceProp prop;
+    cudaError_t e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) { delete h; return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    if (prop.major != 10) {
+        delete h;
+        return fail(DSPSLAM_E_UNSUPPORTED, "libdspslam_sm100 needs a Blackwell (sm_100) device");
+    }
+    h->sm_count = prop.multiProcessorCount;
+    h->dec.L = desc->code_len;
+    h->dec.in_dim = desc->code_len + 3;
+    h->dec.h3 = HID - h->dec.in_dim;
+    h->dec.h3p = (h->dec.h3 + 15) & ~15;
+    int rc = pack_fp32(h, W_host, b_host);
+    if (rc) { dspslam_destroy(h); return rc; }
+    e = simt_configure();
+    if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, std::string("simt_configure: ") + cudaGetErrorString(e)); }
+    e = cudaMalloc(&h->lat, sizeof(float) * (2 * HID + MAX_L + 64));
+    if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
+    if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
+    h->tc_ready = (rc == 0);
+    *out = h;
+    return 0;
+}
+
+void dspslam_destroy(dspslam_handle* h) {
+    if (!h) return;
+    {
+        DeviceGuard g(h->device);
+        cudaDeviceSynchronize();
+        if (h->wblob) cudaFree(h->wblob);
+        if (h->hblob) cudaFree(h->hblob);
+        if (h->ws) cudaFree(h->ws);
+        if (h->lat) cudaFree(h->lat);
+        if (h->zeros) cudaFree(h->zeros);
+    }
+    delete h;
+}
+
+static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
+                   float* sdf_out, float* jac_out) {
+    if (!h || !code || !xyz || !sdf_out || n < 0) return fail(DSPSLAM_E_BADARG, "null/negative argument");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (n == 0) return 0;
+    if (n > ((int64_t)1 << 31) - 256) return fail(DSPSLAM_E_BADARG, "n too large for one call");
+    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    float* c0 = h->lat;
+    float* c4 = h->lat + HID;
+    launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
+    if (mode == DSPSLAM_MODE_FP32) {
+        if (jac_out) launch_sdf_jac_simt(h->dec, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
+        else launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, sdf_out, S(stream));
+    } else {
+        if (jac_out) tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
+        else tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
+    }
+    return check_launch(h, 2, "dspslam_sdf");
+}
+
+int dspslam_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
+                float* sdf_out) {
+    if (!h) return fail(DSPSLAM_E_BADARG, "null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return run_sdf(h, stream, mode, code, xyz, n, sdf_out, nullptr);
+}
+
+int dspslam_sdf_jac(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
+                    float* sdf_out, float* jac_out) {
+    if (!h || !jac_out) return fail(DSPSLAM_E_BADARG, "null handle or jac_out");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return run_sdf(h, stream, mode, code, xyz, n, sdf_out, jac_out);
+}
+
+int dspslam_mean_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
+                     float* mean_out) {
+    if (!h || !mean_out || n <= 0) return fail(DSPSLAM_E_BADARG, "bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    int rc = ensure_ws(h, (size_t)n * sizeof(float));
+    if (rc) return rc;
+    float* tmp = reinterpret_cast<float*>(h->ws);
+    rc = run_sdf(h, stream, mode, code, xyz, n, tmp, nullptr);
+    if (rc) return rc;
+    launch_mean(tmp, n, mean_out, S(stream));
+    return check_launch(h, 1, "dspslam_mean_sdf");
+}
+
+int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* code, int G, int64_t i0,
+                     int64_t i1, int coord_mode, float* out) {
+    if (!h || !code || !out) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (G < 2 || G > 1024) return fail(DSPSLAM_E_BADARG, "G out of range [2,1024]");
+    const int64_t total = (int64_t)G * G * G;
+    if (i0 < 0 || i1 < i0 || i1 > total) return fail(DSPSLAM_E_BADARG, "bad index range");
+    if (coord_mode != DSPSLAM_GRID_REFERENCE_SHEAR && coord_mode != DSPSLAM_GRID_LATTICE)
+        return fail(DSPSLAM_E_BADARG, "bad coord_mode");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (i1 == i0) return 0;
+    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    float* c0 = h->lat;
+    float* c4 = h->lat + HID;
+    launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
+    if (mode == DSPSLAM_MODE_FP32) launch_grid_simt(h->dec, G, i0, i1, coord_mode, c0, c4, out, S(stream));
+    else tc_launch_sdf_rows(h->dec, h->sm_count, nullptr, i1 - i0, i0, G, 1 + coord_mode, c0, c4, out, S(stream));
+    return check_launch(h, 2, "dspslam_grid_sdf");
+}
+
+static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int B,
+                  const int32_t* pts_off, const int32_t* ray_off, const int32_t* n_fg, const float* pts,
+                  const float* rays, const float* depth, int64_t total_pts, int64_t total_rays, int max_pts,
+                  int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
+                  const float* scale_in, int32_t* status_out, float* loss_out, float* dbg_out, int dbg_stride) {
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    if (B <= 0 || B > 65535) return fail(DSPSLAM_E_BADARG, "B must be in 1..65535");
+    if (iters < 0) return fail(DSPSLAM_E_BADARG, "negative iteration count");
+    const int D = prm.D;
+    if (!prm.pose_only && (D < 2 || D > DSP_MAX_D)) return fail(DSPSLAM_E_BADARG, "num_depth_samples must be 2..64");
+    const int64_t V = total_rays * D;
+    if (total_pts + V > ((int64_t)1 << 31) - 1024) return fail(DSPSLAM_E_BADARG, "batch too large: split it");
+    cudaStream_t st = S(stream);
+
+    GnWork w{};
+    w.dec = h->dec;
+    w.prm = prm;
+    w.B = B;
+    w.total_rays = (int)total_rays;
+    w.total_pts = (int)total_pts;
+    w.fgroups_max = (int)(((int64_t)max_rays * D + GROUP_ROWS - 1) / GROUP_ROWS);
+    w.jgroups_max = (int)(((int64_t)max_pts + (int64_t)max_rays * D + GROUP_ROWS - 1) / GROUP_ROWS);
+    if (w.jgroups_max < 1) w.jgroups_max = 1;
+    w.pts_off = pts_off; w.ray_off = ray_off; w.n_fg = n_fg;
+    w.pts = pts; w.rays = rays; w.depth = depth;
+
+    const size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
+    Carver c;
+    const size_t o_st = c.take(sizeof(ObjState) * B);
+    const size_t o_code = c.take(sizeof(float) * MAX_L * B);
+    const size_t o_c0 = c.take(sizeof(float) * HID * B);
+    const size_t o_c4 = c.take(sizeof(float) * HID * B);
+    const size_t o_frows = c.take(sizeof(float4) * (size_t)V);
+    const size_t o_sdf = c.take(sizeof(float) * (size_t)V);
+    const size_t o_rcnt = c.take(sizeof(int) * (size_t)total_rays);
+    const size_t o_roff = c.take(sizeof(int) * (size_t)total_rays);
+    const size_t o_jrows = c.take(sizeof(float4) * (size_t)(total_pts + V));
+    const size_t o_jres = c.take(sizeof(float) * (size_t)(total_pts + V));
+    const size_t o_act = c.take((size_t)total_pts);
+    const size_t o_sres = c.take(sizeof(float) * (size_t)total_pts);
+    const size_t o_tobj = c.take(sizeof(int) * max_tiles);
+    const size_t o_trow = c.take(sizeof(int) * max_tiles);
+    const size_t o_ntl = c.take(sizeof(int) * 8);
+    const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
+    if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
+    int rc = ensure_ws(h, c.off);
+    if (rc) return rc;
+    char* base = h->ws;
+    w.st = reinterpret_cast<ObjState*>(base + o_st);
+    w.code = reinterpret_cast<float*>(base + o_code);
+    w.c0 = reinterpret_cast<float*>(base + o_c0);
+    w.c4 = reinterpret_cast<float*>(base + o_c4);
+    w.frows = reinterpret_cast<float4*>(base + o_frows);
+    w.sdf_samp = reinterpret_cast<float*>(base + o_sdf);
+    w.ray_cnt = reinterpret_cast<int*>(base + o_rcnt);
+    w.ray_roff = reinterpret_cast<int*>(base + o_roff);
+    w.jrows = reinterpret_cast<float4*>(base + o_jrows);
+    w.jres = reinterpret_cast<float*>(base + o_jres);
+    w.active = reinterpret_cast<uint8_t*>(base + o_act);
+    w.sres = reinterpret_cast<float*>(base + o_sres);
+    w.tile_obj = reinterpret_cast<int*>(base + o_tobj);
+    w.tile_row0 = reinterpret_cast<int*>(base + o_trow);
+    w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
+    w.partials = reinterpret_cast<float*>(base + o_part);
+
+    int nl = 0;
+    launch_gn_init(w, pose_in, code_in, h->dec.L, scale_in, st); ++nl;
+    for (int e = 0; e < iters; ++e) {
+        launch_gn_prep(w, e, st); ++nl;
+        if (!prm.pose_only) {
+            launch_gn_sample(w, st); ++nl;
+            if (mode == DSPSLAM_MODE_FP32) { launch_gn_fwd_simt(w, st); ++nl; }
+            else nl += tc_launch_gn_fwd(w, h->sm_count, st);
+            launch_gn_ray_count(w, st); ++nl;
+            launch_gn_rayscan(w, st); ++nl;
+            launch_gn_ray_emit(w, st); ++nl;
+        }
+        if (mode == DSPSLAM_MODE_FP32) { launch_gn_jac_simt(w, st); ++nl; }
+        else nl += tc_launch_gn_jac(w, h->sm_count, st);
+        launch_gn_solve(w, e, dbg_out, dbg_stride, st); ++nl;
+    }
+    launch_gn_final(w, pose_out, code_out, h->dec.L, scale_in, status_out, loss_out, st); ++nl;
+    return check_launch(h, nl, "dspslam_gn");
+}
+
+int dspslam_gn_joint(dspslam_handle* h, void* stream, int mode, const dspslam_joint_params* p, int B,
+                     const int32_t* pts_off, const int32_t* ray_off, const int32_t* n_fg, const float* pts,
+                     const float* rays, const float* depth, int64_t total_pts, int64_t total_rays, int max_pts,
+                     int max_rays, float* t_cam_obj_io, float* code_io, int32_t* status_out, float* loss_out,
+                     float* dbg_out) {
+    if (!h || !p || !pts_off || !ray_off || !n_fg || !t_cam_obj_io || !code_io)
+        return fail(DSPSLAM_E_BADARG, "null argument");
+    if ((total_pts > 0 && !pts) || (total_rays > 0 && (!rays || !depth))) return fail(DSPSLAM_E_BADARG, "null data array");
+    if (total_pts < 0 || total_rays < 0 || max_pts < 0 || max_rays < 0) return fail(DSPSLAM_E_BADARG, "negative size");
+    JointParamsDev prm{};
+    prm.k1 = p->k1; prm.k2 = p->k2; prm.k3 = p->k3; prm.k4 = p->k4;
+    prm.b1 = p->b1; prm.b2 = p->b2; prm.lr = p->lr; prm.s_damp = p->s_damp; prm.th = p->cut_off;
+    prm.D = p->num_depth_samples;
+    prm.pose_only = 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return gn_run(h, stream, mode, prm, p->num_iterations, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
+                  total_rays, max_pts, max_rays, t_cam_obj_io, t_cam_obj_io, code_io, code_io, nullptr, status_out,
+                  loss_out, dbg_out, DSPSLAM_DBG_STRIDE);
+}
+
+int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iterations, int B,
+                         const int32_t* pts_off, const float* pts, int64_t total_pts, int max_pts,
+                         const float* scale, const float* code, float* t_co_se3_io, float* dbg_out) {
+    if (!h || !pts_off || !pts || !scale || !code || !t_co_se3_io) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (total_pts <= 0 || max_pts <= 0 || B <= 0) return fail(DSPSLAM_E_BADARG, "no surface points");
+    JointParamsDev prm{};
+    prm.pose_only = 1;
+    prm.D = 0;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    // the kernels index ray_off / n_fg even without rays: hand them zero arrays
+    if (h->zeros_cap < (size_t)B + 1) {
+        if (h->zeros) { CK(cudaDeviceSynchronize()); CK(cudaFree(h->zeros)); h->zeros = nullptr; h->zeros_cap = 0; }
+        const size_t cap = (size_t)B + 1025;
+        CK(cudaMalloc(&h->zeros, sizeof(int32_t) * cap));
+        CK(cudaMemset(h->zeros, 0, sizeof(int32_t) * cap));
+        h->zeros_cap = cap;
+    }
+    return gn_run(h, stream, mode, prm, num_iterations, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
+                  total_pts, 0, max_pts, 0, t_co_se3_io, t_co_se3_io, code, nullptr, scale, nullptr, nullptr, dbg_out,
+                  64);
+}
+
+}  // extern "C"

@@ -1,0 +1,67 @@
+// Kernel-launcher interface between api.cu and the kernel translation units.
+#pragma once
+#include "common.cuh"
+
+namespace dsp {
+
+// Device view of one Gauss-Newton batch: inputs, state and scratch (all device pointers).
+struct GnWork {
+    DecoderDev dec;
+    JointParamsDev prm;
+    int B;
+    int total_rays, total_pts;
+    int jgroups_max;   // 128-row groups per object in the Jacobian kernel grid / partial slots per object
+    int fgroups_max;   // 128-row groups per object in the forward (ray-sample) kernel grid
+    // inputs
+    const int* pts_off;   // [B+1]
+    const int* ray_off;   // [B+1]
+    const int* n_fg;      // [B]
+    const float* pts;     // [total_pts][3]  camera frame
+    const float* rays;    // [total_rays][3]
+    const float* depth;   // [total_rays]
+    // state
+    ObjState* st;         // [B]
+    float* code;          // [B][MAX_L]
+    float* c0;            // [B][512] latent bias of layer 0
+    float* c4;            // [B][512] latent bias of layer 4
+    // scratch
+    float4* frows;        // [total_rays*D]  compacted in-ball samples per object: x,y,z,dest
+    float* sdf_samp;      // [total_rays*D]  SDF per ray sample (SDF_OUTSIDE outside the ball)
+    int* ray_cnt;         // [total_rays]
+    int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its object
+    float4* jrows;        // [total_pts + total_rays*D]  per object: M surface rows then K render rows: x,y,z,coef
+    float* jres;          // same indexing: residual of render rows
+    uint8_t* active;      // [total_pts]     pose-only inlier flags
+    float* sres;          // [total_pts]     last SDF residual per surface point
+    float* partials;      // [B][jgroups_max][PART_STRIDE]
+    // tcgen05 path work lists (filled by k_gn_plan_*)
+    int* tile_obj;        // [max tiles] object of each 128-row tile
+    int* tile_row0;       // [max tiles] first row of the tile inside the object
+    int* n_tiles;         // [2] number of forward / Jacobian tiles
+};
+
+cudaError_t simt_configure();
+void launch_latent_bias(const DecoderDev& dec, const float* codes, int n_codes, int stride, float* c0,
+                        float* c4, cudaStream_t st);
+void launch_sdf_rows_simt(const DecoderDev& dec, const float* xyz, int64_t n, const float* c0,
+                          const float* c4, float* out, cudaStream_t st);
+void launch_grid_simt(const DecoderDev& dec, int G, int64_t i0, int64_t i1, int coord_mode, const float* c0,
+                      const float* c4, float* out, cudaStream_t st);
+void launch_sdf_jac_simt(const DecoderDev& dec, const float* xyz, int64_t n, const float* c0, const float* c4,
+                         float* sdf_out, float* jac_out, cudaStream_t st);
+void launch_mean(const float* v, int64_t n, float* out, cudaStream_t st);
+
+void launch_gn_init(const GnWork& w, const float* pose_in, const float* code_in, int code_stride,
+                    const float* scale_in, cudaStream_t st);
+void launch_gn_prep(const GnWork& w, int iter, cudaStream_t st);
+void launch_gn_final(const GnWork& w, float* pose_out, float* code_out, int code_stride, const float* scale_in,
+                     int* status_out, float* loss_out, cudaStream_t st);
+void launch_gn_sample(const GnWork& w, cudaStream_t st);
+void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st);
+void launch_gn_ray_count(const GnWork& w, cudaStream_t st);
+void launch_gn_ray_emit(const GnWork& w, cudaStream_t st);
+void launch_gn_rayscan(const GnWork& w, cudaStream_t st);
+void launch_gn_jac_simt(const GnWork& w, cudaStream_t st);
+void launch_gn_solve(const GnWork& w, int iter, float* dbg, int dbg_stride, cudaStream_t st);
+
+}  // namespace dsp

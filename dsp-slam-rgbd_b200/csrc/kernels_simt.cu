@@ -1,0 +1,692 @@
+// FP32 (validation-mode) kernels and the mode-independent Gauss-Newton kernels of
+// libdspslam_sm100.  See common.cuh / mlp_simt.cuh / hd_math.h for the pieces and
+// include/dspslam.h for the reference lines each entry point replaces.
+#include "kernels.h"
+#include "mlp_simt.cuh"
+
+namespace dsp {
+
+// ---------------------------------------------------------------------------
+// latent bias:  c0 = b0 + W0[:, :L] z   and   c4 = b4 + W4[:, h3:h3+L] z   (one CTA per code)
+// ---------------------------------------------------------------------------
+__global__ void k_latent_bias(DecoderDev dec, const float* __restrict__ codes, int code_stride,
+                              float* __restrict__ c0, float* __restrict__ c4) {
+    __shared__ float z[MAX_L];
+    const int b = blockIdx.x;
+    if (threadIdx.x < dec.L) z[threadIdx.x] = codes[(size_t)b * code_stride + threadIdx.x];
+    __syncthreads();
+    for (int n = threadIdx.x; n < HID; n += blockDim.x) {
+        float s0 = 0.f, s4 = 0.f;
+        for (int l = 0; l < dec.L; ++l) {
+            s0 = fmaf(__ldg(dec.Wt0 + (size_t)l * HID + n), z[l], s0);
+            s4 = fmaf(__ldg(dec.W4in + (size_t)l * HID + n), z[l], s4);
+        }
+        c0[(size_t)b * HID + n] = s0 + __ldg(dec.bias[0] + n);
+        c4[(size_t)b * HID + n] = s4 + __ldg(dec.bias[4] + n);
+    }
+}
+
+// reference-shear / lattice voxel coordinates from the linear index (utils.py:97-116)
+__device__ __forceinline__ void grid_coord(int64_t i, int G, int coord_mode, float& x, float& y, float& z) {
+    const float vs = (float)(2.0 / (double)(G - 1));
+    const float Gf = (float)G;
+    const float zi = (float)(i % G);
+    float xi, yi;
+    if (coord_mode == 0) {
+        const float q = __fdiv_rn(__ll2float_rn(i), Gf);
+        yi = fmodf(q, Gf);
+        xi = fmodf(__fdiv_rn(q, Gf), Gf);
+    } else {
+        yi = (float)((i / G) % G);
+        xi = (float)((i / ((int64_t)G * G)) % G);
+    }
+    x = __fadd_rn(__fmul_rn(xi, vs), -1.f);
+    y = __fadd_rn(__fmul_rn(yi, vs), -1.f);
+    z = __fadd_rn(__fmul_rn(zi, vs), -1.f);
+}
+
+// ---------------------------------------------------------------------------
+// forward-only SDF of n rows with one code.  SRC 0: xyz array, SRC 1: voxel grid index
+// ---------------------------------------------------------------------------
+template <int SRC>
+__global__ void __launch_bounds__(simt::NT, 1)
+k_sdf_rows_simt(DecoderDev dec, const float* __restrict__ xyz, int64_t n, int64_t i0, int G,
+                int coord_mode, const float* __restrict__ c0, const float* __restrict__ c4,
+                float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    simt::Smem& sm = *reinterpret_cast<simt::Smem*>(smem_raw);
+    const int tid = threadIdx.x;
+    const int64_t row0 = (int64_t)blockIdx.x * GROUP_ROWS;
+    for (int sub = 0; sub < GROUP_ROWS / simt::TM; ++sub) {
+        const int64_t r0 = row0 + sub * simt::TM;
+        if (r0 >= n) break;
+        if (tid < simt::TM) {
+            const int64_t r = r0 + tid;
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (r < n) {
+                if (SRC == 0) {
+                    x = xyz[r * 3 + 0]; y = xyz[r * 3 + 1]; z = xyz[r * 3 + 2];
+                } else {
+                    grid_coord(i0 + r, G, coord_mode, x, y, z);
+                }
+            }
+            sm.xyz0[tid][0] = x; sm.xyz0[tid][1] = y; sm.xyz0[tid][2] = z; sm.xyz0[tid][3] = 0.f;
+        }
+        __syncthreads();
+        simt::forward32<false>(sm, dec, c0, c4);
+        if (tid < simt::TM && r0 + tid < n) out[r0 + tid] = sm.sdf[tid];
+        __syncthreads();
+    }
+}
+
+// SDF + d sdf / d [code | xyz] of n rows with one code
+__global__ void __launch_bounds__(simt::NT, 1)
+k_sdf_jac_simt(DecoderDev dec, const float* __restrict__ xyz, int64_t n, const float* __restrict__ c0,
+               const float* __restrict__ c4, float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    simt::Smem& sm = *reinterpret_cast<simt::Smem*>(smem_raw);
+    const int tid = threadIdx.x;
+    const int64_t row0 = (int64_t)blockIdx.x * GROUP_ROWS;
+    const int in_dim = dec.in_dim;
+    for (int sub = 0; sub < GROUP_ROWS / simt::TM; ++sub) {
+        const int64_t r0 = row0 + sub * simt::TM;
+        if (r0 >= n) break;
+        if (tid < simt::TM) {
+            const int64_t r = r0 + tid;
+            float x = 0.f, y = 0.f, z = 0.f;
+            if (r < n) { x = xyz[r * 3 + 0]; y = xyz[r * 3 + 1]; z = xyz[r * 3 + 2]; }
+            sm.xyz0[tid][0] = x; sm.xyz0[tid][1] = y; sm.xyz0[tid][2] = z; sm.xyz0[tid][3] = 0.f;
+        }
+        __syncthreads();
+        simt::forward32<true>(sm, dec, c0, c4);
+        simt::backward32(sm, dec);
+        if (tid < simt::TM && r0 + tid < n) sdf_out[r0 + tid] = sm.sdf[tid];
+        for (int e = tid; e < simt::TM * in_dim; e += simt::NT) {
+            const int row = e / in_dim, i = e - row * in_dim;
+            if (r0 + row < n) jac_out[(r0 + row) * in_dim + i] = sm.jac[row][i];
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_mean(const float* __restrict__ v, int64_t n, float* __restrict__ out) {
+    __shared__ double red[32];
+    double s = 0.0;
+    for (int64_t i = threadIdx.x; i < n; i += blockDim.x) s += (double)v[i];
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+        out[0] = (float)(t / (double)n);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Gauss-Newton: init / prep / final
+// ---------------------------------------------------------------------------
+__global__ void k_gn_init(GnWork w, const float* __restrict__ pose_in, const float* __restrict__ code_in,
+                          int code_in_stride, const float* __restrict__ scale_in) {
+    const int b = blockIdx.x;
+    ObjState& s = w.st[b];
+    const int M = w.pts_off[b + 1] - w.pts_off[b];
+    if (threadIdx.x == 0) {
+        float T[16];
+        for (int i = 0; i < 16; ++i) T[i] = pose_in[(size_t)b * 16 + i];
+        if (w.prm.pose_only) {                       // optimizer.py:54-56
+            const float sc = scale_in[b];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) T[i * 4 + j] *= sc;
+        }
+        inv_affine(T, s.T_oc);
+        s.status = 0; s.n_valid = 0; s.K = 0; s.M_active = M;
+        s.sdf_loss = 0.f; s.render_loss = 0.f; s.loss = 0.f;
+    }
+    for (int l = threadIdx.x; l < w.dec.L; l += blockDim.x)
+        w.code[(size_t)b * MAX_L + l] = code_in[(size_t)b * code_in_stride + l];
+    for (int p = threadIdx.x; p < M; p += blockDim.x) w.active[w.pts_off[b] + p] = 1;
+}
+
+// once per iteration and object: pose-derived scalars, latent biases, surface rows
+__global__ void k_gn_prep(GnWork w, int iter) {
+    __shared__ float z[MAX_L];
+    __shared__ int cnt;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int p0 = w.pts_off[b], M = w.pts_off[b + 1] - p0;
+    if (tid == 0) {
+        inv_affine(s.T_oc, s.T_co);
+        float A[9];
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) A[i * 3 + j] = s.T_co[i * 4 + j];
+        const float sc = powf(det3(A), 1.0f / 3.0f);          // optimizer.py:123
+        s.scale = sc;
+        s.dmin = s.T_co[11] - 1.0f * sc;                       // optimizer.py:125
+        s.dmax = s.T_co[11] + 1.0f * sc;
+        s.rot_res = w.prm.pose_only ? 0.f : rot_prior(s.T_co, sc, s.rotJ);
+        s.n_valid = 0;
+        s.K = 0;
+        cnt = 0;
+    }
+    if (tid < w.dec.L) z[tid] = w.code[(size_t)b * MAX_L + tid];
+    __syncthreads();
+    for (int n = tid; n < HID; n += blockDim.x) {
+        float s0 = 0.f, s4 = 0.f;
+        for (int l = 0; l < w.dec.L; ++l) {
+            s0 = fmaf(__ldg(w.dec.Wt0 + (size_t)l * HID + n), z[l], s0);
+            s4 = fmaf(__ldg(w.dec.W4in + (size_t)l * HID + n), z[l], s4);
+        }
+        w.c0[(size_t)b * HID + n] = s0 + __ldg(w.dec.bias[0] + n);
+        w.c4[(size_t)b * HID + n] = s4 + __ldg(w.dec.bias[4] + n);
+    }
+    // pose-only inlier cut after iteration e == 4 (optimizer.py:77-79)
+    const bool cut = w.prm.pose_only && iter == 5;
+    const size_t jb = (size_t)p0 + (size_t)w.ray_off[b] * w.prm.D;
+    int local = 0;
+    for (int p = tid; p < M; p += blockDim.x) {
+        const float* q = w.pts + (size_t)(p0 + p) * 3;
+        float x, y, zz;
+        sample_point(s.T_oc, q[0], q[1], q[2], 1.0f, x, y, zz);
+        uint8_t a = w.active[p0 + p];
+        if (cut && a) {
+            a = (fabsf(w.sres[p0 + p]) <= 0.05f) ? 1 : 0;
+            w.active[p0 + p] = a;
+        }
+        local += a;
+        w.jrows[jb + p] = make_float4(x, y, zz, a ? 1.f : 0.f);
+    }
+    if (cut) {
+        atomicAdd(&cnt, local);
+        __syncthreads();
+        if (tid == 0) s.M_active = cnt;
+    }
+}
+
+__global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __restrict__ code_out,
+                           int code_out_stride, const float* __restrict__ scale_in,
+                           int* __restrict__ status_out, float* __restrict__ loss_out) {
+    const int b = blockIdx.x;
+    const ObjState& s = w.st[b];
+    if (threadIdx.x == 0) {
+        float T[16];
+        inv_affine(s.T_oc, T);
+        if (w.prm.pose_only) {                       // optimizer.py:84-85
+            const float sc = scale_in[b];
+            for (int i = 0; i < 3; ++i)
+                for (int j = 0; j < 3; ++j) T[i * 4 + j] /= sc;
+        }
+        for (int i = 0; i < 16; ++i) pose_out[(size_t)b * 16 + i] = T[i];
+        if (status_out) status_out[b] = s.status;
+        if (loss_out) loss_out[b] = s.loss;
+    }
+    if (code_out)
+        for (int l = threadIdx.x; l < w.dec.L; l += blockDim.x)
+            code_out[(size_t)b * code_out_stride + l] = w.code[(size_t)b * MAX_L + l];
+}
+
+// ---------------------------------------------------------------------------
+// render term: sample generation (one warp per ray), loss.py:74-84
+// ---------------------------------------------------------------------------
+__global__ void k_gn_sample(GnWork w) {
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (warp >= w.total_rays) return;
+    const int b = find_segment(w.ray_off, w.B, warp);
+    ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int D = w.prm.D;
+    const float rx = w.rays[(size_t)warp * 3 + 0], ry = w.rays[(size_t)warp * 3 + 1],
+                rz = w.rays[(size_t)warp * 3 + 2];
+    const size_t fbase = (size_t)w.ray_off[b] * D;      // this object's region of frows
+    for (int j0 = 0; j0 < D; j0 += 32) {
+        const int j = j0 + lane;
+        bool valid = false;
+        float x = 0.f, y = 0.f, z = 0.f;
+        if (j < D) {
+            const float d = linspace_at(s.dmin, s.dmax, D, j);
+            sample_point(s.T_oc, rx, ry, rz, d, x, y, z);
+            const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+            valid = nrm < 1.0f;                          // loss.py:82
+            if (!valid) w.sdf_samp[(size_t)warp * D + j] = SDF_OUTSIDE;
+        }
+        const unsigned ball = __ballot_sync(0xffffffffu, valid);
+        int base = 0;
+        if (lane == 0 && ball) base = atomicAdd(&s.n_valid, __popc(ball));
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (valid) {
+            const int off = __popc(ball & ((1u << lane) - 1u));
+            w.frows[fbase + base + off] = make_float4(x, y, z, __int_as_float(warp * D + j));
+        }
+    }
+}
+
+// forward-only SDF of the compacted in-ball samples, FP32 path (grid: groups x objects)
+__global__ void __launch_bounds__(simt::NT, 1) k_gn_fwd_simt(GnWork w) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    simt::Smem& sm = *reinterpret_cast<simt::Smem*>(smem_raw);
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int n = s.n_valid;
+    const int row0 = blockIdx.x * GROUP_ROWS;
+    if (row0 >= n) return;
+    const size_t fbase = (size_t)w.ray_off[b] * w.prm.D;
+    const float* c0 = w.c0 + (size_t)b * HID;
+    const float* c4 = w.c4 + (size_t)b * HID;
+    for (int sub = 0; sub < GROUP_ROWS / simt::TM; ++sub) {
+        const int r0 = row0 + sub * simt::TM;
+        if (r0 >= n) break;
+        int dest = -1;
+        if (tid < simt::TM) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (r0 + tid < n) { v = w.frows[fbase + r0 + tid]; dest = __float_as_int(v.w); }
+            sm.xyz0[tid][0] = v.x; sm.xyz0[tid][1] = v.y; sm.xyz0[tid][2] = v.z; sm.xyz0[tid][3] = 0.f;
+        }
+        __syncthreads();
+        simt::forward32<false>(sm, w.dec, c0, c4);
+        if (dest >= 0) w.sdf_samp[dest] = sm.sdf[tid];
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------------------
+// render term: per-ray scan (thread per ray), count then emit.  loss.py:98-155
+// ---------------------------------------------------------------------------
+template <bool EMIT>
+__global__ void k_gn_ray(GnWork w) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= w.total_rays) return;
+    const int b = find_segment(w.ray_off, w.B, r);
+    const ObjState& s = w.st[b];
+    if (s.status != 0) { if (!EMIT) w.ray_cnt[r] = 0; return; }
+    const int D = w.prm.D;
+    RayParams p;
+    p.th = w.prm.th; p.dmin = s.dmin; p.dmax = s.dmax; p.D = D;
+    const int local = r - w.ray_off[b];
+    const float dobs = (local < w.n_fg[b]) ? w.depth[r] : 1.1f * s.dmax;   // optimizer.py:128
+    const float* sdf = w.sdf_samp + (size_t)r * D;
+    if (!EMIT) {
+        w.ray_cnt[r] = ray_scan(sdf, 1, dobs, p, [](int, float, float) {});
+    } else {
+        const int M = w.pts_off[b + 1] - w.pts_off[b];
+        size_t at = (size_t)w.pts_off[b] + (size_t)w.ray_off[b] * D + M + w.ray_roff[r];
+        const float rx = w.rays[(size_t)r * 3 + 0], ry = w.rays[(size_t)r * 3 + 1], rz = w.rays[(size_t)r * 3 + 2];
+        ray_scan(sdf, 1, dobs, p, [&](int k, float de_ds, float res) {
+            float x, y, z;
+            sample_point(s.T_oc, rx, ry, rz, linspace_at(s.dmin, s.dmax, D, k), x, y, z);
+            w.jrows[at] = make_float4(x, y, z, de_ds);
+            w.jres[at] = res;
+            ++at;
+        });
+    }
+}
+template __global__ void k_gn_ray<false>(GnWork);
+template __global__ void k_gn_ray<true>(GnWork);
+
+// exclusive scan of the per-ray row counts of one object (CTA per object) + status
+__global__ void k_gn_rayscan(GnWork w) {
+    __shared__ int warp_sums[32];
+    __shared__ int carry;
+    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int r0 = w.ray_off[b], N = w.ray_off[b + 1] - r0;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < N; base += blockDim.x) {
+        const int i = base + tid;
+        const int v = (i < N) ? w.ray_cnt[r0 + i] : 0;
+        int inc = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) warp_sums[wid] = inc;
+        __syncthreads();
+        if (wid == 0) {
+            int ws = (lane < (int)(blockDim.x >> 5)) ? warp_sums[lane] : 0;
+            int winc = ws;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, winc, o);
+                if (lane >= o) winc += t;
+            }
+            warp_sums[lane] = winc - ws;                // exclusive warp offsets
+            if (lane == 31) warp_sums[31] = winc;       // (blockDim <= 992: slot 31 free) total of this chunk
+        }
+        __syncthreads();
+        const int chunk_total = warp_sums[31];
+        if (i < N) w.ray_roff[r0 + i] = carry + warp_sums[wid] + inc - v;
+        __syncthreads();
+        if (tid == 0) carry += chunk_total;
+        __syncthreads();
+    }
+    if (tid == 0) {
+        s.K = carry;
+        if (s.n_valid < 10) s.status = 1;               // loss.py:87-88
+        else if (carry == 0) s.status = 2;              // mean over 0 rows = NaN (optimizer.py:150-152)
+    }
+}
+
+// ---------------------------------------------------------------------------
+// SDF + Jacobian rows -> J^T J / J^T r partial sums, FP32 path (grid: groups x objects)
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ void build_pose_row(float* J, float gx, float gy, float gz, float x, float y, float z) {
+    // d x_o / d xi = [I | -hat(x) | x]  (loss_utils.py:176-195)
+    J[0] = gx; J[1] = gy; J[2] = gz;
+    J[3] = y * gz - z * gy;
+    J[4] = z * gx - x * gz;
+    J[5] = x * gy - y * gx;
+    J[6] = gx * x + gy * y + gz * z;
+}
+
+__global__ void __launch_bounds__(simt::NT, 1) k_gn_jac_simt(GnWork w) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    simt::Smem& sm = *reinterpret_cast<simt::Smem*>(smem_raw);
+    __shared__ float red[2][8];
+    const int b = blockIdx.y, g = blockIdx.x, tid = threadIdx.x;
+    const ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int p0 = w.pts_off[b], M = w.pts_off[b + 1] - p0;
+    const int K = w.prm.pose_only ? 0 : s.K;
+    const int rows = M + K;
+    const int row0 = g * GROUP_ROWS;
+    if (row0 >= rows) return;
+    const size_t jb = (size_t)p0 + (size_t)w.ray_off[b] * w.prm.D;
+    const float* c0 = w.c0 + (size_t)b * HID;
+    const float* c4 = w.c4 + (size_t)b * HID;
+    const int L = w.dec.L, n = POSE + L;
+    const float w_s = (w.prm.pose_only ? 1.f : w.prm.k2) / (float)s.M_active;
+    const float w_r = w.prm.k1 / (float)K;
+    constexpr int NQ = (HMAX * HMAX + HMAX + simt::NT - 1) / simt::NT;   // 20
+    float acc[NQ];
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) acc[q] = 0.f;
+    float ls = 0.f, lr = 0.f;
+    for (int sub = 0; sub < GROUP_ROWS / simt::TM; ++sub) {
+        const int r0 = row0 + sub * simt::TM;
+        if (r0 >= rows) break;
+        if (tid < simt::TM) {
+            const int r = r0 + tid;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            float res = 0.f;
+            if (r < rows) {
+                v = w.jrows[jb + r];
+                if (r >= M) res = w.jres[jb + r];
+            }
+            sm.xyz0[tid][0] = v.x; sm.xyz0[tid][1] = v.y; sm.xyz0[tid][2] = v.z; sm.xyz0[tid][3] = 0.f;
+            sm.coef[tid] = v.w;
+            sm.res[tid] = res;
+        }
+        __syncthreads();
+        simt::forward32<true>(sm, w.dec, c0, c4);
+        simt::backward32(sm, w.dec);
+        // J rows (pose 7 | code L) into sm.gin
+        if (tid < simt::TM) {
+            const int r = r0 + tid;
+            const float coef = sm.coef[tid];
+            const float x = sm.xyz0[tid][0], y = sm.xyz0[tid][1], z = sm.xyz0[tid][2];
+            build_pose_row(sm.gin[tid], coef * sm.jac[tid][L], coef * sm.jac[tid][L + 1],
+                           coef * sm.jac[tid][L + 2], x, y, z);
+            float wr = 0.f, rt = 0.f;
+            if (r < rows) {
+                if (r < M) {                                   // surface row: residual = SDF itself
+                    const float sd = sm.sdf[tid];
+                    w.sres[p0 + r] = sd;
+                    rt = w.prm.pose_only ? sd : huber_res(sd, w.prm.b2);
+                    if (coef != 0.f) { wr = w_s; ls += rt * rt; }
+                } else {                                       // render row
+                    rt = huber_res(sm.res[tid], w.prm.b1);
+                    wr = w_r;
+                    lr += rt * rt;
+                }
+            }
+            sm.wrow[tid] = wr;
+            sm.rt[tid] = rt;
+        }
+        for (int e = tid; e < simt::TM * L; e += simt::NT) {
+            const int row = e / L, j = e - row * L;
+            sm.gin[row][POSE + j] = sm.coef[row] * sm.jac[row][j];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < NQ; ++q) {
+            const int e = tid + q * simt::NT;
+            if (e < n * n) {
+                const int i = e / n, j = e - i * n;
+                float a = acc[q];
+                for (int row = 0; row < simt::TM; ++row)
+                    a = fmaf(sm.wrow[row] * sm.gin[row][i], sm.gin[row][j], a);
+                acc[q] = a;
+            } else if (e < n * n + n) {
+                const int i = e - n * n;
+                float a = acc[q];
+                for (int row = 0; row < simt::TM; ++row)
+                    a = fmaf(-sm.wrow[row] * sm.gin[row][i], sm.rt[row], a);
+                acc[q] = a;
+            }
+        }
+        __syncthreads();
+    }
+    float* part = w.partials + ((size_t)b * w.jgroups_max + g) * PART_STRIDE;
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const int e = tid + q * simt::NT;
+        if (e < n * n + n) part[e] = acc[q];
+    }
+    // loss sums live in lanes 0..31 of warp 0 only
+    if (tid < 32) {
+        for (int o = 16; o > 0; o >>= 1) {
+            ls += __shfl_xor_sync(0xffffffffu, ls, o);
+            lr += __shfl_xor_sync(0xffffffffu, lr, o);
+        }
+        if (tid == 0) { part[PART_LOSS] = ls; part[PART_LOSS + 1] = lr; }
+    }
+    (void)red;
+}
+
+// ---------------------------------------------------------------------------
+// normal equations: reduce partials, priors + damping, Cholesky solve, update.
+// optimizer.py:157-194 (joint) / :69-75 (pose only).  One CTA per object.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gn_solve(GnWork w, int iter, float* __restrict__ dbg, int dbg_stride) {
+    __shared__ double Hs[(HMAX + 1) * HMAX];
+    __shared__ double xs[HMAX + 1];
+    __shared__ float losses[2];
+    __shared__ int fail;
+    const int b = blockIdx.x, tid = threadIdx.x;
+    ObjState& s = w.st[b];
+    float* dbg_o = dbg ? dbg + ((size_t)iter * w.B + b) * dbg_stride : nullptr;
+    const int L = w.dec.L, n = POSE + L;
+    if (s.status != 0) {
+        if (dbg_o && tid == 0 && !w.prm.pose_only) {
+            dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
+            dbg_o[PART_LOSS + 5] = (float)s.status;
+        }
+        return;
+    }
+    const int M = w.pts_off[b + 1] - w.pts_off[b];
+    const int K = w.prm.pose_only ? 0 : s.K;
+    const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;
+    const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
+    for (int e = tid; e < n * n + n; e += blockDim.x) {
+        double a = 0.0;
+        for (int g = 0; g < ng; ++g) a += (double)part[(size_t)g * PART_STRIDE + e];
+        Hs[e] = a;                      // rows 0..n-1: H, row n: b
+    }
+    if (tid < 2) {
+        float a = 0.f;
+        for (int g = 0; g < ng; ++g) a += part[(size_t)g * PART_STRIDE + PART_LOSS + tid];
+        losses[tid] = a / (tid == 0 ? (float)s.M_active : (float)K);     // mean of robust_res^2
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const float sl = losses[0], rl = w.prm.pose_only ? 0.f : losses[1];
+        fail = (sl != sl) || (rl != rl);                 // math.isnan checks (optimizer.py:137,151)
+        if (!fail) { s.sdf_loss = sl; s.render_loss = rl; }
+    }
+    __syncthreads();
+    if (fail) {
+        if (tid == 0) { s.status = 2; if (dbg_o && !w.prm.pose_only) dbg_o[PART_LOSS + 5] = 2.f; }
+        return;
+    }
+    int dim;
+    if (!w.prm.pose_only) {
+        dim = n;
+        if (tid < L) {                                                  // code prior (optimizer.py:172-174)
+            Hs[(POSE + tid) * n + POSE + tid] += (double)w.prm.k3;
+            Hs[n * n + POSE + tid] -= (double)w.prm.k3 * (double)w.code[(size_t)b * MAX_L + tid];
+        }
+        if (tid == 64) {                                                // rotation prior (:177-181)
+            for (int i = 0; i < 3; ++i) {
+                for (int j = 0; j < 3; ++j)
+                    Hs[(3 + i) * n + 3 + j] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rotJ[j];
+                Hs[n * n + 3 + i] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rot_res;
+            }
+        }
+        __syncthreads();
+        if (tid < POSE) Hs[tid * n + tid] += 1.0 + (tid == POSE - 1 ? (double)w.prm.s_damp : 0.0);   // :185-186
+    } else {
+        dim = 6;
+        // move b (row n) next to the 6x6 block as row 6 so that the factorisation below sees [H; b^T]
+        if (tid < 6) xs[tid] = Hs[n * n + tid];
+        __syncthreads();
+        if (tid < 6) { Hs[6 * n + tid] = xs[tid]; Hs[tid * n + tid] += 1e-2; }          // :71
+    }
+    __syncthreads();
+    if (dbg_o) {
+        if (!w.prm.pose_only) {
+            for (int e = tid; e < n * n + n; e += blockDim.x) dbg_o[e] = (float)Hs[e];
+            if (tid == 0) {
+                dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
+                dbg_o[PART_LOSS + 2] = s.sdf_loss; dbg_o[PART_LOSS + 3] = s.render_loss;
+                dbg_o[PART_LOSS + 4] = s.scale;    dbg_o[PART_LOSS + 5] = 0.f;
+            }
+        } else if (tid < 42) {
+            dbg_o[tid] = (float)Hs[(tid / 6) * n + (tid % 6)];          // 6x6 H then b
+            if (tid == 0) dbg_o[42] = (float)s.M_active;
+        }
+        __syncthreads();
+    }
+    // Cholesky of H with b^T carried as row `dim`:  afterwards row dim holds y = L^-1 b
+    for (int j = 0; j < dim; ++j) {
+        if (tid == 0) Hs[j * n + j] = sqrt(Hs[j * n + j]);
+        __syncthreads();
+        const double d = Hs[j * n + j];
+        for (int i = j + 1 + tid; i <= dim; i += blockDim.x) Hs[i * n + j] /= d;
+        __syncthreads();
+        const int cnt = dim - j;                        // rows j+1 .. dim
+        for (int e = tid; e < cnt * cnt; e += blockDim.x) {
+            const int i = j + 1 + e / cnt, k = j + 1 + e % cnt;
+            if (k <= i && k < dim) Hs[i * n + k] -= Hs[i * n + j] * Hs[k * n + j];
+        }
+        __syncthreads();
+    }
+    // back substitution L^T x = y  (warp 0)
+    if (tid < 32) {
+        for (int j = dim - 1; j >= 0; --j) {
+            double a = 0.0;
+            for (int i = j + 1 + tid; i < dim; i += 32) a += Hs[i * n + j] * xs[i];
+            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+            if (tid == 0) xs[j] = (Hs[dim * n + j] - a) / Hs[j * n + j];
+            __syncwarp();
+        }
+    }
+    __syncthreads();
+    // update (optimizer.py:189-194 / :73-75)
+    if (tid == 0) {
+        float dp[7], dT[16], Tn[16];
+        if (!w.prm.pose_only) {
+            for (int i = 0; i < 7; ++i) dp[i] = w.prm.lr * (float)xs[i];
+            exp_sim3(dp, dT);
+        } else {
+            for (int i = 0; i < 6; ++i) dp[i] = (float)xs[i];
+            exp_se3(dp, dT);
+        }
+        mul_affine(dT, s.T_oc, Tn);
+        for (int i = 0; i < 16; ++i) s.T_oc[i] = Tn[i];
+        if (!w.prm.pose_only) s.loss = w.prm.k1 * s.render_loss + w.prm.k2 * s.sdf_loss;
+        else s.loss = s.sdf_loss;
+    }
+    if (!w.prm.pose_only && tid < L)
+        w.code[(size_t)b * MAX_L + tid] += w.prm.lr * (float)xs[POSE + tid];
+}
+
+// ---------------------------------------------------------------------------
+// launchers
+// ---------------------------------------------------------------------------
+static size_t simt_smem() { return sizeof(simt::Smem); }
+
+cudaError_t simt_configure() {
+    cudaError_t e;
+    const int bytes = (int)simt_smem();
+    if ((e = cudaFuncSetAttribute(k_sdf_rows_simt<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(k_sdf_rows_simt<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(k_sdf_jac_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(k_gn_fwd_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(k_gn_jac_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    return cudaSuccess;
+}
+
+void launch_latent_bias(const DecoderDev& dec, const float* codes, int n_codes, int stride, float* c0,
+                        float* c4, cudaStream_t st) {
+    k_latent_bias<<<n_codes, 256, 0, st>>>(dec, codes, stride, c0, c4);
+}
+
+void launch_sdf_rows_simt(const DecoderDev& dec, const float* xyz, int64_t n, const float* c0,
+                          const float* c4, float* out, cudaStream_t st) {
+    const unsigned grid = (unsigned)((n + GROUP_ROWS - 1) / GROUP_ROWS);
+    k_sdf_rows_simt<0><<<grid, simt::NT, simt_smem(), st>>>(dec, xyz, n, 0, 0, 0, c0, c4, out);
+}
+
+void launch_grid_simt(const DecoderDev& dec, int G, int64_t i0, int64_t i1, int coord_mode, const float* c0,
+                      const float* c4, float* out, cudaStream_t st) {
+    const int64_t n = i1 - i0;
+    const unsigned grid = (unsigned)((n + GROUP_ROWS - 1) / GROUP_ROWS);
+    k_sdf_rows_simt<1><<<grid, simt::NT, simt_smem(), st>>>(dec, nullptr, n, i0, G, coord_mode, c0, c4, out);
+}
+
+void launch_sdf_jac_simt(const DecoderDev& dec, const float* xyz, int64_t n, const float* c0, const float* c4,
+                         float* sdf_out, float* jac_out, cudaStream_t st) {
+    const unsigned grid = (unsigned)((n + GROUP_ROWS - 1) / GROUP_ROWS);
+    k_sdf_jac_simt<<<grid, simt::NT, simt_smem(), st>>>(dec, xyz, n, c0, c4, sdf_out, jac_out);
+}
+
+void launch_mean(const float* v, int64_t n, float* out, cudaStream_t st) { k_mean<<<1, 1024, 0, st>>>(v, n, out); }
+
+void launch_gn_init(const GnWork& w, const float* pose_in, const float* code_in, int code_stride,
+                    const float* scale_in, cudaStream_t st) {
+    k_gn_init<<<w.B, 128, 0, st>>>(w, pose_in, code_in, code_stride, scale_in);
+}
+void launch_gn_prep(const GnWork& w, int iter, cudaStream_t st) { k_gn_prep<<<w.B, 256, 0, st>>>(w, iter); }
+void launch_gn_final(const GnWork& w, float* pose_out, float* code_out, int code_stride, const float* scale_in,
+                     int* status_out, float* loss_out, cudaStream_t st) {
+    k_gn_final<<<w.B, 64, 0, st>>>(w, pose_out, code_out, code_stride, scale_in, status_out, loss_out);
+}
+void launch_gn_sample(const GnWork& w, cudaStream_t st) {
+    if (w.total_rays == 0) return;
+    const int64_t threads = (int64_t)w.total_rays * 32;
+    k_gn_sample<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(w);
+}
+void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st) {
+    if (w.fgroups_max == 0) return;
+    k_gn_fwd_simt<<<dim3(w.fgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);
+}
+void launch_gn_ray_count(const GnWork& w, cudaStream_t st) {
+    if (w.total_rays == 0) return;
+    k_gn_ray<false><<<(w.total_rays + 127) / 128, 128, 0, st>>>(w);
+}
+void launch_gn_ray_emit(const GnWork& w, cudaStream_t st) {
+    if (w.total_rays == 0) return;
+    k_gn_ray<true><<<(w.total_rays + 127) / 128, 128, 0, st>>>(w);
+}
+void launch_gn_rayscan(const GnWork& w, cudaStream_t st) { k_gn_rayscan<<<w.B, 256, 0, st>>>(w); }
+void launch_gn_jac_simt(const GnWork& w, cudaStream_t st) {
+    k_gn_jac_simt<<<dim3(w.jgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);
+}
+void launch_gn_solve(const GnWork& w, int iter, float* dbg, int dbg_stride, cudaStream_t st) {
+    k_gn_solve<<<w.B, 256, 0, st>>>(w, iter, dbg, dbg_stride);
+}
+
+}  // namespace dsp

@@ -1,0 +1,22 @@
+// tcgen05 (FP16 operands, FP32 TMEM accumulators) decoder kernels: interface to api.cu.
+#pragma once
+#include "kernels.h"
+
+namespace dsp {
+
+// Packs the FP16 operand tiles, uploads them (device pointer in *hblob, also recorded in dec)
+// and sets the kernels' shared-memory attributes.  Returns 0 on success.
+int tc_pack_and_configure(DecoderDev& dec, const float* const* W_host, const float* const* b_host,
+                          __half** hblob);
+const char* tc_last_error();
+
+// src_mode 0: xyz array; 1: voxel grid, reference shear; 2: voxel grid, lattice
+void tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, int64_t i0, int G,
+                        int src_mode, const float* c0, const float* c4, float* out, cudaStream_t st);
+void tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
+                       const float* c4, float* sdf_out, float* jac_out, cudaStream_t st);
+// return the number of kernels launched
+int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st);
+int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st);
+
+}  // namespace dsp

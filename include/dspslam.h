@@ -1,0 +1,142 @@
+/* libdspslam_sm100.so - C ABI of the B200-native DSP-SLAM object-reconstruction hot path.
+ *
+ * Every entry point replaces a piece of the reference's Python/PyTorch path
+ * (paths relative to the reference repository):
+ *
+ *   dspslam_create / dspslam_destroy   deep_sdf/workspace.py:202-223 (decoder upload, once per process)
+ *   dspslam_sdf                        reconstruct/loss_utils.py:51-79   decode_sdf
+ *   dspslam_sdf_jac                    reconstruct/loss_utils.py:82-113  get_batch_sdf_jacobian
+ *   dspslam_mean_sdf                   reconstruct/optimizer.py:207-213 + loss.py:46-56
+ *   dspslam_grid_sdf                   reconstruct/optimizer.py:224-227 + utils.py:97-116 (voxel grid + decode_sdf)
+ *   dspslam_gn_joint                   reconstruct/optimizer.py:90-205   Optimizer.reconstruct_object
+ *                                      (+ loss.py:22-43, 60-166, 169-192; loss_utils.py:176-275)
+ *   dspslam_gn_pose_only               reconstruct/optimizer.py:46-87    Optimizer.estimate_pose_cam_obj
+ *
+ * Conventions
+ *   - plain C types only; all array arguments are DEVICE pointers unless the name
+ *     ends in _host; `stream` is a cudaStream_t passed as void* (0 = default stream).
+ *   - matrices are row-major float32; poses are 4x4 (16 floats).
+ *   - every function returns 0 on success or a DSPSLAM_E_* code; the message of the
+ *     last error on the calling thread is returned by dspslam_last_error().
+ *   - no exception crosses the ABI; nothing is retained from caller memory after return
+ *     (asynchronous work is ordered on `stream`).
+ *   - a handle may be used from several host threads; calls on one handle serialise
+ *     on an internal mutex (the reference serialises on the Python GIL).
+ */
+#ifndef DSPSLAM_H_
+#define DSPSLAM_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSPSLAM_ABI_VERSION 1
+
+enum {
+    DSPSLAM_OK = 0,
+    DSPSLAM_E_BADARG = 1,
+    DSPSLAM_E_CUDA = 2,
+    DSPSLAM_E_NOMEM = 3,
+    DSPSLAM_E_UNSUPPORTED = 4
+};
+
+/* arithmetic mode of the decoder contractions */
+enum {
+    DSPSLAM_MODE_FP32 = 0, /* FP32 FFMA validation mode (1e-5 parity)                    */
+    DSPSLAM_MODE_TC = 1    /* tcgen05 tensor cores, FP16 operands / FP32 TMEM accumulate */
+};
+
+/* per-object status written by the Gauss-Newton drivers */
+enum {
+    DSPSLAM_ST_OK = 0,
+    DSPSLAM_ST_FEW_POINTS = 1, /* < 10 ray samples inside the unit ball (loss.py:87-88)       */
+    DSPSLAM_ST_NAN = 2         /* NaN loss, e.g. no render row survived (optimizer.py:137,151) */
+};
+
+enum { DSPSLAM_GRID_REFERENCE_SHEAR = 0, DSPSLAM_GRID_LATTICE = 1 };
+
+typedef struct dspslam_handle dspslam_handle;
+
+/* Decoder geometry.  Supported family: in = [code(code_len) | xyz(3)], `n_hidden` = 8 layers of
+ * `hidden` = 512 units, the input re-injected at layer `latent_in` = 4 (so layer 3 emits
+ * hidden - (code_len+3) features), ReLU, one output with a final tanh.  */
+typedef struct {
+    int32_t code_len;  /* 1..64 */
+    int32_t hidden;    /* 512   */
+    int32_t n_hidden;  /* 8     */
+    int32_t latent_in; /* 4     */
+} dspslam_decoder_desc;
+
+/* Effective (weight-norm folded) FP32 parameters on the HOST, natural nn.Linear layout
+ * W[k] is [out_k][in_k] row-major, b[k] is [out_k], k = 0..n_hidden (9 layers). */
+int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
+                   const float* const* b_host, int device, dspslam_handle** out);
+void dspslam_destroy(dspslam_handle* h);
+const char* dspslam_last_error(void);
+int dspslam_abi_version(void);
+/* number of kernels launched by this handle so far (for bench.py's gpu_launches) */
+int64_t dspslam_launch_count(const dspslam_handle* h);
+
+/* sdf_out[i] = decoder([code, xyz[i]]),  i < n   (one code shared by all rows, as decode_sdf does) */
+int dspslam_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz,
+                int64_t n, float* sdf_out);
+
+/* additionally jac_out[i][0..code_len+3) = d sdf / d [code, xyz]  (row stride code_len+3) */
+int dspslam_sdf_jac(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz,
+                    int64_t n, float* sdf_out, float* jac_out);
+
+/* mean_out[0] = mean_i sdf(code, xyz[i])   (device scalar) */
+int dspslam_mean_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
+                     const float* xyz, int64_t n, float* mean_out);
+
+/* SDF over linear grid indices [i0, i1) of a G^3 grid over [-1,1]^3 (x slowest, z fastest);
+ * out[i - i0].  coord_mode: DSPSLAM_GRID_REFERENCE_SHEAR reproduces the reference's
+ * true-division grid, DSPSLAM_GRID_LATTICE the regular lattice. */
+int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* code, int G,
+                     int64_t i0, int64_t i1, int coord_mode, float* out);
+
+/* Hyper-parameters of the joint optimisation (configs/config_*.json "optimizer") */
+typedef struct {
+    float k1, k2, k3, k4; /* render, sdf, code-prior, rotation-prior weights */
+    float b1, b2;         /* Huber thresholds: render, sdf                    */
+    float lr;             /* learning_rate                                    */
+    float s_damp;         /* scale_damping                                    */
+    float cut_off;        /* cut_off_threshold (occupancy band)               */
+    int32_t num_iterations;
+    int32_t num_depth_samples; /* <= 64 */
+    int32_t reserved;
+} dspslam_joint_params;
+
+/* A batch of B independent detections, concatenated.
+ *   pts_off[B+1]  offsets (in points) into pts;   ray_off[B+1] offsets (in rays) into rays/depth
+ *   n_fg[B]       number of foreground rays of each object (the first n_fg rays carry a depth)
+ *   pts[sum M][3] surface points, camera frame;  rays[sum N][3];  depth[sum N] (background entries ignored)
+ *   t_cam_obj_io[B][16]  in: initial object->camera Sim(3); out: optimised
+ *   code_io[B][code_len] in: initial code; out: optimised
+ *   status_out[B] int32, loss_out[B] float (k1*render + k2*sdf of the last iteration)
+ *   dbg_out: NULL or [num_iterations][B][DSPSLAM_DBG_STRIDE] floats: H (71x71 row-major), b (71),
+ *            then K, n_valid, sdf_loss, render_loss, scale, status per iteration.
+ */
+#define DSPSLAM_POSE_DIM 7
+#define DSPSLAM_DBG_STRIDE 5120
+
+int dspslam_gn_joint(dspslam_handle* h, void* stream, int mode, const dspslam_joint_params* prm,
+                     int B, const int32_t* pts_off, const int32_t* ray_off, const int32_t* n_fg,
+                     const float* pts, const float* rays, const float* depth,
+                     int64_t total_pts, int64_t total_rays, int max_pts, int max_rays,
+                     float* t_cam_obj_io, float* code_io, int32_t* status_out, float* loss_out,
+                     float* dbg_out);
+
+/* Pose-only optimisation: t_co_se3_io[B][16] SE(3) in/out, scale[B], code[B][code_len] fixed.
+ * dbg_out: NULL or [num_iterations][B][64]: H (6x6), b (6), M_active. */
+int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iterations, int B,
+                         const int32_t* pts_off, const float* pts, int64_t total_pts, int max_pts,
+                         const float* scale, const float* code, float* t_co_se3_io,
+                         float* dbg_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSPSLAM_H_ */

@@ -229,13 +229,12 @@ def compute_sdf_loss(dec, pts_cam, T_oc, code):
 
 def linspace_torch(a, b, n, dtype=np.float32):
     """torch.linspace's symmetric evaluation (start + i*step for the lower half,
-    end - (n-1-i)*step for the upper half)."""
-    a, b = dtype(a), dtype(b)
-    step = (b - a) / dtype(n - 1)
+    end - (n-1-i)*step for the upper half), evaluated in double and rounded once,
+    which is what torch's CPU kernel returns for a float32 result."""
+    a, b = float(dtype(a)), float(dtype(b))
+    step = (b - a) / (n - 1)
     i = np.arange(n)
-    lo = a + step * i.astype(dtype)
-    hi = b - step * (n - 1 - i).astype(dtype)
-    return np.where(i < n // 2, lo, hi).astype(dtype)
+    return np.where(i < n // 2, a + step * i, b - step * (n - 1 - i)).astype(dtype)
 
 
 def compute_render_loss(dec, rays, depth_obs, T_oc, sampled_depth, code, th=0.01,
