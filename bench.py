@@ -1,0 +1,326 @@
+#!/usr/bin/env python
+"""Benchmark of the B200 DSP-SLAM object-reconstruction hot path (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--mode tc|fp32]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Workload (`config.workload`): BASELINE.json configs[1] = "C2", a KITTI stereo+LiDAR frame batch of 16 car
+detections x 2048 surface points + 2248 rays x 50 depth samples, 10 Gauss-Newton iterations
+(SURVEY.md 8(d)), synthetic detections and the W-fit synthetic decoder (assets/).  One STEP = one pass of
+the hot path (`dspslam_gn_joint`: all 10 iterations) over one batch of 16 detections per GPU.  With N GPUs
+every rank optimises its own 16 detections (independent objects, no collective: weak scaling).
+
+  value     objects/s with the batch already resident in HBM (device-timed with CUDA events, max over ranks)
+  e2e       objects/s through the reference-shaped API `Optimizer.reconstruct_objects` with HOST numpy
+            arrays: packing, pinned H2D, the GN loop and the D2H of poses/codes inside the timed region
+  roofline  the dominant kernel (forward-only decoder over the in-ball ray samples of the render term):
+            algorithmic FLOP (3 671 040 per query) / its CUDA-event time measured live inside the timed
+            region via dspslam_profile_*; peak = MEASURED_PEAKS.json bf16 dense (sustained figure: the
+            kernel is timed inside a long step).
+  cpu_baseline  the numpy oracle port of the reference's algorithm timed on this box's host cores on a
+            bounded sample of the same workload (rank 0, N = 1 only).
+
+`--impl reference` times the CPU implementation alone (the reference is Python/PyTorch and cannot travel
+to the GPU box; the oracle port restates it, see oracle/dspslam_oracle.py) and prints the same JSON line.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "dsp-slam-rgbd_b200"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+FLOP_FWD = 3_671_040          # forward-only SDF query  
+FLOP_JAC = 7_342_080          # SDF + Jacobian query
+OBJ_PER_RANK = 16
+M_PTS, N_BG, D_SAMPLES, ITERS = 2048, 200, 50, 10
+METRIC = "objects_reconstructed_per_s"
+
+
+def workload_desc():
+    return ("C2: KITTI stereo+LiDAR frame batch, %d car detections/GPU x %d surface pts + %d rays x %d depth "
+            "samples, %d GN iters" % (OBJ_PER_RANK, M_PTS, M_PTS + N_BG, D_SAMPLES, ITERS))
+
+
+def make_dets(rank, n=OBJ_PER_RANK):
+    from dspslam import synth
+    return [synth.make_kitti_detection(rank * OBJ_PER_RANK + k, M=M_PTS, n_bg=N_BG) for k in range(n)]
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.isfile(path):
+        with open(path) as f:
+            p = json.load(f)
+        return dict(tflops=float(p.get("bf16_tflops_sustained", p.get("bf16_tflops", 1590.0))),
+                    hbm=float(p.get("hbm_gbs", 6650.0)), src="measured (MEASURED_PEAKS.json, bf16 sustained)")
+    return dict(tflops=1400.0, hbm=6650.0, src="fallback (B200_PROFILING.md)")
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampling (nvidia-smi during the timed region)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        threading.Thread(target=self._read, daemon=True).start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 <= t <= t1 + 0.2 and len(r) >= 7] or [r for _, r in self.rows if len(r) >= 7]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[0]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
+                "samples": len(rows), "power_w_max": max(float(r[2]) for r in rows)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the numpy oracle port of the reference algorithm
+# ------------------------------------------------------------------------------------------------
+def cpu_threads():
+    try:
+        from threadpoolctl import threadpool_info
+        n = max([i.get("num_threads", 1) for i in threadpool_info()] or [1])
+        return int(n)
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_cpu_sample(n_obj, iters):
+    """Times `n_obj` C2-shaped detections for `iters` GN iterations on the host cores; returns (objects/s at the
+    full 10 iterations, seconds spent, threads)."""
+    from dspslam import synth
+    from oracle import dspslam_oracle as orc
+    dec = synth.load_wfit()
+    cfg = synth.kitti_config()
+    cfg.optimizer.joint_optim.num_iterations = iters
+    opt = orc.OracleOptimizer(orc.OracleDecoder(dec.state_dict()), cfg)
+    dets = make_dets(0, n_obj)
+    t0 = time.perf_counter()
+    for d in dets:
+        opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
+    dt = time.perf_counter() - t0
+    per_obj_full = dt / n_obj * (ITERS / iters)
+    return 1.0 / per_obj_full, dt, cpu_threads()
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    # warm-up (BLAS thread pools, page-in) on a tiny case, then K bounded steps
+    run_cpu_sample(1, 1)
+    vals, secs = [], 0.0
+    for _ in range(max(1, args.steps)):
+        v, dt, thr = run_cpu_sample(1, 2)
+        vals.append(v)
+        secs += dt
+    v = float(np.median(vals))
+    sample = "1 detection x 2 of %d GN iterations per step (scaled to %d), %d steps" % (ITERS, ITERS, len(vals))
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "objects/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * OBJ_PER_RANK / v,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_desc(), "impl": "numpy oracle port of reconstruct/optimizer.py on host cores"},
+            "cpu_baseline": {"value": v, "unit": "objects/s", "cores": thr, "kind": "port", "sample": sample},
+            "e2e": {"value": v, "unit": "objects/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def ours_arm(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from dspslam import synth
+    from reconstruct.optimizer import Optimizer
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    dec = synth.load_wfit()
+    cfg = synth.kitti_config()
+    opt = Optimizer(dec, cfg, mode=args.mode, device=local_rank)
+    eng = opt.engine
+    prm = opt._params()
+    dets = make_dets(rank)
+    batch = eng.upload_joint(eng.pack_joint(dets))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
+
+    # ---- device-resident timing -------------------------------------------------------------
+    for _ in range(max(3, args.warmup)):
+        eng.run_joint(batch, prm)
+    res = eng.download_joint(batch)
+    n_good = int((res.status == 0).sum())
+    eng.profile_enable(True)
+    sampler = ClockSampler(local_rank)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    l0 = eng.launches
+    barrier()
+    if rank == 0:
+        sampler.start()
+    t_wall0 = time.time()
+    for a, b in ev:
+        flush.fill_(1)                                   # L2 flush between steps (untimed)
+        a.record()
+        eng.run_joint(batch, prm)
+        b.record()
+    barrier()
+    t_wall1 = time.time()
+    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    launches = eng.launches - l0
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    dev_ms = max_over_ranks(float(np.sum(step_ms)))
+    prof = eng.profile_read()
+    eng.profile_enable(False)
+
+    # ---- end to end through the reference-shaped API (host arrays in, host arrays out) --------
+    for _ in range(2):
+        opt.reconstruct_objects(dets)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        outs = opt.reconstruct_objects(dets)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e_good = sum(1 for o in outs if o.is_good)
+
+    total_obj = OBJ_PER_RANK * world * args.steps
+    value = total_obj / (dev_ms * 1e-3)
+    pk = peaks()
+    fwd_flop = prof["rows_gn_fwd"] * FLOP_FWD
+    jac_flop = prof["rows_gn_jac"] * FLOP_JAC
+    fwd_tf = fwd_flop / (prof["ms_gn_fwd"] * 1e-3) / 1e12 if prof["ms_gn_fwd"] > 0 else 0.0
+    jac_tf = jac_flop / (prof["ms_gn_jac"] * 1e-3) / 1e12 if prof["ms_gn_jac"] > 0 else 0.0
+    rows_fwd_all = sum_over_ranks(prof["rows_gn_fwd"])
+    rows_jac_all = sum_over_ranks(prof["rows_gn_jac"])
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    line = {
+        "metric": METRIC, "value": value, "unit": "objects/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None,
+        "dtype": "f16 operands, f32 accumulate (tcgen05)" if args.mode == "tc" else "f32",
+        "data": "synthetic",
+        "config": {"workload": workload_desc(), "mode": args.mode, "objects_per_gpu": OBJ_PER_RANK,
+                   "decoder": "DeepSDF 8x512, code 64, W-fit synthetic weights",
+                   "l2": "flushed between steps (256 MiB fill, untimed); each step times one dspslam_gn_joint"},
+        "e2e": {"value": total_obj / e2e_s, "unit": "objects/s", "h2d_bytes_per_step": int(batch.h2d_bytes),
+                "d2h_bytes_per_step": int(batch.d2h_bytes)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": "forward-only decoder over in-ball ray samples (GN render term)",
+                     "achieved": fwd_tf, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": fwd_tf / pk["tflops"],
+                     "traffic": None, "peak_source": pk["src"],
+                     "avg_launch_ms": prof["ms_gn_fwd"] / max(1, prof["n_gn_fwd"]),
+                     "rows_per_launch": prof["rows_gn_fwd"] / max(1, prof["n_gn_fwd"]),
+                     "share_of_step": prof["ms_gn_fwd"] / max(1e-9, float(np.sum(step_ms)))},
+        "roofline_jacobian": {"bound": "tensor", "kernel": "fused decoder forward + input-gradient sweep + JtJ/Jtr",
+                              "achieved": jac_tf, "peak": pk["tflops"], "unit": "TFLOP/s",
+                              "frac": jac_tf / pk["tflops"],
+                              "avg_launch_ms": prof["ms_gn_jac"] / max(1, prof["n_gn_jac"]),
+                              "rows_per_launch": prof["rows_gn_jac"] / max(1, prof["n_gn_jac"]),
+                              "share_of_step": prof["ms_gn_jac"] / max(1e-9, float(np.sum(step_ms)))},
+        "mquery_per_s": {"forward": rows_fwd_all / (dev_ms * 1e-3) / 1e6,
+                         "sdf_jacobian": rows_jac_all / (dev_ms * 1e-3) / 1e6,
+                         "forward_kernel_only": prof["rows_gn_fwd"] / max(1e-9, prof["ms_gn_fwd"] * 1e-3) / 1e6,
+                         "sdf_jacobian_kernel_only": prof["rows_gn_jac"] / max(1e-9, prof["ms_gn_jac"] * 1e-3) / 1e6},
+        "objects_good": {"resident": n_good, "e2e": e2e_good, "of": OBJ_PER_RANK},
+    }
+    if world == 1 and not args.no_cpu:
+        run_cpu_sample(1, 1)
+        v, dt, thr = run_cpu_sample(1, 3)
+        line["cpu_baseline"] = {"value": v, "unit": "objects/s", "cores": thr, "kind": "port",
+                                "sample": "1 detection x 3 of %d GN iterations, scaled to %d (%.1f s of CPU work)"
+                                          % (ITERS, ITERS, dt)}
+    else:
+        line["cpu_baseline"] = None
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="tc", choices=["tc", "fp32"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        reference_arm(args, rank, world)
+        return
+    if world == 1 and args.gpus > 1:
+        # launched without torchrun: re-launch under torch.distributed.run
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(29500 + os.getpid() % 2000), os.path.abspath(__file__)] + sys.argv[1:]
+        sys.exit(subprocess.call(cmd))
+    ours_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

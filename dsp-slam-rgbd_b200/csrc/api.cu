@@ -40,6 +40,12 @@ struct dspslam_handle {
     int64_t launches = 0;
     bool tc_ready = false;
     std::mutex mu;
+    // profiling (dspslam_profile_*): event pairs around decoder launches + device row counters
+    bool prof_on = false;
+    std::vector<cudaEvent_t> prof_ev;      // pool, used in pairs
+    std::vector<int> prof_kind;            // kind of each recorded pair
+    std::vector<int64_t> prof_rows;        // host-known row count of the pair (stand-alone launches)
+    unsigned long long* stats = nullptr;   // device: [0] GN forward rows, [1] GN Jacobian rows
 };
 
 namespace {
@@ -148,6 +154,26 @@ int check_launch(dspslam_handle* h, int n_launch, const char* what) {
     return 0;
 }
 
+enum { PK_GN_FWD = 0, PK_GN_JAC = 1, PK_ROWS_FWD = 2, PK_ROWS_JAC = 3 };
+
+// records the start event of a profiled launch group; returns the pair index or -1
+int prof_begin(dspslam_handle* h, int kind, int64_t rows, cudaStream_t st) {
+    if (!h->prof_on) return -1;
+    const size_t pair = h->prof_kind.size();
+    while (h->prof_ev.size() < 2 * (pair + 1)) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) { (void)cudaGetLastError(); return -1; }
+        h->prof_ev.push_back(e);
+    }
+    h->prof_kind.push_back(kind);
+    h->prof_rows.push_back(rows);
+    cudaEventRecord(h->prof_ev[2 * pair], st);
+    return (int)pair;
+}
+void prof_end(dspslam_handle* h, int pair, cudaStream_t st) {
+    if (pair >= 0) cudaEventRecord(h->prof_ev[2 * pair + 1], st);
+}
+
 struct DeviceGuard {
     int prev = -1;
     explicit DeviceGuard(int dev) {
@@ -198,6 +224,9 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, std::string("simt_configure: ") + cudaGetErrorString(e)); }
     e = cudaMalloc(&h->lat, sizeof(float) * (2 * HID + MAX_L + 64));
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    e = cudaMalloc(&h->stats, sizeof(unsigned long long) * 8);
+    if (e == cudaSuccess) e = cudaMemset(h->stats, 0, sizeof(unsigned long long) * 8);
+    if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
@@ -215,20 +244,24 @@ void dspslam_destroy(dspslam_handle* h) {
         if (h->ws) cudaFree(h->ws);
         if (h->lat) cudaFree(h->lat);
         if (h->zeros) cudaFree(h->zeros);
+        if (h->stats) cudaFree(h->stats);
+        for (cudaEvent_t e : h->prof_ev) cudaEventDestroy(e);
     }
     delete h;
 }
 
 static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
                    float* sdf_out, float* jac_out) {
-    if (!h || !code || !xyz || !sdf_out || n < 0) return fail(DSPSLAM_E_BADARG, "null/negative argument");
+    if (!h || n < 0) return fail(DSPSLAM_E_BADARG, "null/negative argument");
     if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
-    if (n == 0) return 0;
+    if (n == 0) return 0;                       // empty query: nothing to do (pointers may be null)
+    if (!code || !xyz || !sdf_out) return fail(DSPSLAM_E_BADARG, "null argument");
     if (n > ((int64_t)1 << 31) - 256) return fail(DSPSLAM_E_BADARG, "n too large for one call");
     if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
     float* c0 = h->lat;
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
+    const int pp = prof_begin(h, jac_out ? PK_ROWS_JAC : PK_ROWS_FWD, n, S(stream));
     if (mode == DSPSLAM_MODE_FP32) {
         if (jac_out) launch_sdf_jac_simt(h->dec, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
         else launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, sdf_out, S(stream));
@@ -236,6 +269,7 @@ static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
         if (jac_out) tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
         else tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
     }
+    prof_end(h, pp, S(stream));
     return check_launch(h, 2, "dspslam_sdf");
 }
 
@@ -285,8 +319,10 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     float* c0 = h->lat;
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
+    const int pp = prof_begin(h, PK_ROWS_FWD, i1 - i0, S(stream));
     if (mode == DSPSLAM_MODE_FP32) launch_grid_simt(h->dec, G, i0, i1, coord_mode, c0, c4, out, S(stream));
     else tc_launch_sdf_rows(h->dec, h->sm_count, nullptr, i1 - i0, i0, G, 1 + coord_mode, c0, c4, out, S(stream));
+    prof_end(h, pp, S(stream));
     return check_launch(h, 2, "dspslam_grid_sdf");
 }
 
@@ -355,6 +391,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.tile_row0 = reinterpret_cast<int*>(base + o_trow);
     w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
     w.partials = reinterpret_cast<float*>(base + o_part);
+    w.stats = h->prof_on ? h->stats : nullptr;
 
     int nl = 0;
     launch_gn_init(w, pose_in, code_in, h->dec.L, scale_in, st); ++nl;
@@ -362,14 +399,18 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
         launch_gn_prep(w, e, st); ++nl;
         if (!prm.pose_only) {
             launch_gn_sample(w, st); ++nl;
+            const int pf = prof_begin(h, PK_GN_FWD, 0, st);
             if (mode == DSPSLAM_MODE_FP32) { launch_gn_fwd_simt(w, st); ++nl; }
             else nl += tc_launch_gn_fwd(w, h->sm_count, st);
+            prof_end(h, pf, st);
             launch_gn_ray_count(w, st); ++nl;
             launch_gn_rayscan(w, st); ++nl;
             launch_gn_ray_emit(w, st); ++nl;
         }
+        const int pj = prof_begin(h, PK_GN_JAC, 0, st);
         if (mode == DSPSLAM_MODE_FP32) { launch_gn_jac_simt(w, st); ++nl; }
         else nl += tc_launch_gn_jac(w, h->sm_count, st);
+        prof_end(h, pj, st);
         launch_gn_solve(w, e, dbg_out, dbg_stride, st); ++nl;
     }
     launch_gn_final(w, pose_out, code_out, h->dec.L, scale_in, status_out, loss_out, st); ++nl;
@@ -418,6 +459,49 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
     return gn_run(h, stream, mode, prm, num_iterations, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
                   total_pts, 0, max_pts, 0, t_co_se3_io, t_co_se3_io, code, nullptr, scale, nullptr, nullptr, dbg_out,
                   64);
+}
+
+int dspslam_profile_enable(dspslam_handle* h, int on) {
+    if (!h) return fail(DSPSLAM_E_BADARG, "null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    CK(cudaDeviceSynchronize());
+    h->prof_on = on != 0;
+    h->prof_kind.clear();
+    h->prof_rows.clear();
+    CK(cudaMemset(h->stats, 0, sizeof(unsigned long long) * 8));
+    return 0;
+}
+
+int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
+    if (!h || !out) return fail(DSPSLAM_E_BADARG, "null argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    memset(out, 0, sizeof(*out));
+    double ms[4] = {0, 0, 0, 0};
+    int64_t rows[4] = {0, 0, 0, 0}, cnt[4] = {0, 0, 0, 0};
+    for (size_t p = 0; p < h->prof_kind.size(); ++p) {
+        CK(cudaEventSynchronize(h->prof_ev[2 * p + 1]));
+        float t = 0.f;
+        CK(cudaEventElapsedTime(&t, h->prof_ev[2 * p], h->prof_ev[2 * p + 1]));
+        const int k = h->prof_kind[p];
+        ms[k] += t;
+        rows[k] += h->prof_rows[p];
+        cnt[k] += 1;
+    }
+    unsigned long long st[8];
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(st, h->stats, sizeof(st), cudaMemcpyDeviceToHost));
+    CK(cudaMemset(h->stats, 0, sizeof(st)));
+    h->prof_kind.clear();
+    h->prof_rows.clear();
+    out->ms_gn_fwd = ms[PK_GN_FWD]; out->ms_gn_jac = ms[PK_GN_JAC];
+    out->ms_rows_fwd = ms[PK_ROWS_FWD]; out->ms_rows_jac = ms[PK_ROWS_JAC];
+    out->rows_gn_fwd = (int64_t)st[0]; out->rows_gn_jac = (int64_t)st[1];
+    out->rows_fwd = rows[PK_ROWS_FWD]; out->rows_jac = rows[PK_ROWS_JAC];
+    out->n_gn_fwd = cnt[PK_GN_FWD]; out->n_gn_jac = cnt[PK_GN_JAC];
+    out->n_rows_fwd = cnt[PK_ROWS_FWD]; out->n_rows_jac = cnt[PK_ROWS_JAC];
+    return 0;
 }
 
 }  // extern "C"

@@ -38,6 +38,7 @@ struct GnWork {
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object
     int* n_tiles;         // [2] number of forward / Jacobian tiles
+    unsigned long long* stats;  // null or [2]: algorithmic rows evaluated (forward-only, SDF+Jacobian)
 };
 
 cudaError_t simt_configure();

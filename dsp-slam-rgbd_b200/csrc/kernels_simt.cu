@@ -508,6 +508,10 @@ __global__ void __launch_bounds__(256) k_gn_solve(GnWork w, int iter, float* __r
     }
     const int M = w.pts_off[b + 1] - w.pts_off[b];
     const int K = w.prm.pose_only ? 0 : s.K;
+    if (w.stats && tid == 0) {
+        atomicAdd(w.stats + 0, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
+        atomicAdd(w.stats + 1, (unsigned long long)(s.M_active + K));
+    }
     const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;
     const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
     for (int e = tid; e < n * n + n; e += blockDim.x) {

@@ -20,7 +20,7 @@ ABI_VERSION = 1
 EXPORTS = [
     "dspslam_abi_version", "dspslam_last_error", "dspslam_launch_count", "dspslam_create",
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
-    "dspslam_gn_joint", "dspslam_gn_pose_only",
+    "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
 ]
 
 
@@ -34,6 +34,12 @@ class JointParams(C.Structure):
                 ("b1", C.c_float), ("b2", C.c_float), ("lr", C.c_float), ("s_damp", C.c_float),
                 ("cut_off", C.c_float), ("num_iterations", C.c_int32),
                 ("num_depth_samples", C.c_int32), ("reserved", C.c_int32)]
+
+
+class Profile(C.Structure):
+    _fields_ = [(n, C.c_double) for n in ("ms_gn_fwd", "ms_gn_jac", "ms_rows_fwd", "ms_rows_jac")] + \
+               [(n, C.c_int64) for n in ("rows_gn_fwd", "rows_gn_jac", "rows_fwd", "rows_jac",
+                                         "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac")]
 
 
 class NativeError(RuntimeError):
@@ -75,6 +81,10 @@ def lib():
                                    i64, i64, C.c_int, C.c_int, fp, fp, fp, fp, fp]
     L.dspslam_gn_pose_only.restype = C.c_int
     L.dspslam_gn_pose_only.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, fp, fp, i64, C.c_int, fp, fp, fp, fp]
+    L.dspslam_profile_enable.restype = C.c_int
+    L.dspslam_profile_enable.argtypes = [vp, C.c_int]
+    L.dspslam_profile_read.restype = C.c_int
+    L.dspslam_profile_read.argtypes = [vp, C.POINTER(Profile)]
     if L.dspslam_abi_version() != ABI_VERSION:
         raise NativeError("libdspslam_sm100.so ABI version mismatch")
     _lib = L

@@ -82,6 +82,15 @@ class Engine:
     def launches(self):
         return int(self.lib.dspslam_launch_count(self._h))
 
+    def profile_enable(self, on=True):
+        N.check(self.lib.dspslam_profile_enable(self._h, 1 if on else 0), "dspslam_profile_enable")
+
+    def profile_read(self):
+        """dict of per-kernel-class device time [ms], rows and launch counts since the last read."""
+        p = N.Profile()
+        N.check(self.lib.dspslam_profile_read(self._h, C.byref(p)), "dspslam_profile_read")
+        return {n: getattr(p, n) for n, _ in N.Profile._fields_}
+
     # -- helpers ------------------------------------------------------------------------------
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)

@@ -11,6 +11,7 @@
  *   dspslam_gn_joint                   reconstruct/optimizer.py:90-205   Optimizer.reconstruct_object
  *                                      (+ loss.py:22-43, 60-166, 169-192; loss_utils.py:176-275)
  *   dspslam_gn_pose_only               reconstruct/optimizer.py:46-87    Optimizer.estimate_pose_cam_obj
+ *   dspslam_profile_enable / _read     reconstruct/loss_utils.py:278-283 get_time (the reference's only timing hook)
  *
  * Conventions
  *   - plain C types only; all array arguments are DEVICE pointers unless the name
@@ -135,6 +136,22 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
                          const int32_t* pts_off, const float* pts, int64_t total_pts, int max_pts,
                          const float* scale, const float* code, float* t_co_se3_io,
                          float* dbg_out);
+
+/* Per-kernel-class device timing (CUDA events recorded on the caller's stream around the decoder
+ * kernels) and algorithmic row counters, for bench.py's roofline.  Replaces the reference's wall-clock
+ * `get_time()` prints.  Off by default; enabling it costs two event records per decoder launch.
+ *   ms_*     summed event time of the forward-only decoder launches of the GN loop (ray samples), the
+ *            SDF+Jacobian launches of the GN loop, and the stand-alone sdf / sdf_jac / grid launches
+ *   rows_*   rows those launches were asked to evaluate (GN: in-ball samples; active surface + render rows)
+ *   n_*      number of launches in each class
+ * dspslam_profile_read synchronises the recorded events, returns the totals since the last read and resets. */
+typedef struct {
+    double ms_gn_fwd, ms_gn_jac, ms_rows_fwd, ms_rows_jac;
+    int64_t rows_gn_fwd, rows_gn_jac, rows_fwd, rows_jac;
+    int64_t n_gn_fwd, n_gn_jac, n_rows_fwd, n_rows_jac;
+} dspslam_profile;
+int dspslam_profile_enable(dspslam_handle* h, int on);
+int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out);
 
 #ifdef __cplusplus
 }
