@@ -262,15 +262,17 @@ static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
     const int pp = prof_begin(h, jac_out ? PK_ROWS_JAC : PK_ROWS_FWD, n, S(stream));
+    int nl = 1;
     if (mode == DSPSLAM_MODE_FP32) {
         if (jac_out) launch_sdf_jac_simt(h->dec, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
         else launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, sdf_out, S(stream));
+        ++nl;
     } else {
-        if (jac_out) tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
-        else tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
+        if (jac_out) nl += tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
+        else nl += tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
     }
     prof_end(h, pp, S(stream));
-    return check_launch(h, 2, "dspslam_sdf");
+    return check_launch(h, nl, "dspslam_sdf");
 }
 
 int dspslam_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
@@ -320,10 +322,11 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
     const int pp = prof_begin(h, PK_ROWS_FWD, i1 - i0, S(stream));
+    int nl = 2;
     if (mode == DSPSLAM_MODE_FP32) launch_grid_simt(h->dec, G, i0, i1, coord_mode, c0, c4, out, S(stream));
-    else tc_launch_sdf_rows(h->dec, h->sm_count, nullptr, i1 - i0, i0, G, 1 + coord_mode, c0, c4, out, S(stream));
+    else nl = 1 + tc_launch_sdf_rows(h->dec, h->sm_count, nullptr, i1 - i0, i0, G, 1 + coord_mode, c0, c4, out, S(stream));
     prof_end(h, pp, S(stream));
-    return check_launch(h, 2, "dspslam_grid_sdf");
+    return check_launch(h, nl, "dspslam_grid_sdf");
 }
 
 static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int B,
@@ -371,6 +374,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_trow = c.take(sizeof(int) * max_tiles);
     const size_t o_ntl = c.take(sizeof(int) * 8);
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
+    const size_t o_xtra = c.take(mode == DSPSLAM_MODE_TC ? tc_xtra_bytes_per_object() * (size_t)B : 0);
     if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
     int rc = ensure_ws(h, c.off);
     if (rc) return rc;
@@ -392,6 +396,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
     w.partials = reinterpret_cast<float*>(base + o_part);
     w.stats = h->prof_on ? h->stats : nullptr;
+    w.tc_xtra = reinterpret_cast<uint8_t*>(base + o_xtra);
 
     int nl = 0;
     launch_gn_init(w, pose_in, code_in, h->dec.L, scale_in, st); ++nl;

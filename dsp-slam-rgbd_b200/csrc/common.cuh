@@ -38,9 +38,9 @@ struct DecoderDev {
     // backward (natural) ---------------------------------------------------
     const float* Wn[8];  // Wn[1],Wn[2],Wn[5..7]: [512][512]; Wn[3]: [h3p][512] (zero rows >= h3);
                          // Wn[4]: [512][512], cols [0,h3) hidden | [h3,512) input; Wn[0] unused (Wt0 serves)
-    // tcgen05 FP16 operand tiles (see mlp_tc.cuh); null until packed
-    const __half* tc_fwd;   // forward B tiles
-    const __half* tc_bwd;   // backward B tiles
+    // tcgen05 path (kernels_tc.cu); null until packed
+    const uint8_t* tc_blob;  // FP16 weight stage images (forward program, then backward program)
+    uint8_t* tc_xtra1;       // extras record (layers 0 and 4) of the single-code entry points
 };
 
 // Per-object Gauss-Newton state (one per detection in the batch).
@@ -63,6 +63,25 @@ struct JointParamsDev {
     int D;
     int pose_only;    // 1: estimate_pose_cam_obj semantics (6 dof, raw residual, damping 1e-2)
 };
+
+// reference-shear / lattice voxel coordinates from the linear index (utils.py:97-116)
+__device__ __forceinline__ void grid_coord(int64_t i, int G, int coord_mode, float& x, float& y, float& z) {
+    const float vs = (float)(2.0 / (double)(G - 1));
+    const float Gf = (float)G;
+    const float zi = (float)(i % G);
+    float xi, yi;
+    if (coord_mode == 0) {
+        const float q = __fdiv_rn(__ll2float_rn(i), Gf);
+        yi = fmodf(q, Gf);
+        xi = fmodf(__fdiv_rn(q, Gf), Gf);
+    } else {
+        yi = (float)((i / G) % G);
+        xi = (float)((i / ((int64_t)G * G)) % G);
+    }
+    x = __fadd_rn(__fmul_rn(xi, vs), -1.f);
+    y = __fadd_rn(__fmul_rn(yi, vs), -1.f);
+    z = __fadd_rn(__fmul_rn(zi, vs), -1.f);
+}
 
 __device__ __forceinline__ int find_segment(const int* __restrict__ off, int n_seg, int idx) {
     // largest b with off[b] <= idx  (off has n_seg+1 entries, off[0] = 0)

@@ -38,6 +38,7 @@ struct GnWork {
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object
     int* n_tiles;         // [2] number of forward / Jacobian tiles
+    uint8_t* tc_xtra;     // [B][2][16 KB] per-object extra blocks of layers 0 and 4 (kernels_tc.cu)
     unsigned long long* stats;  // null or [2]: algorithmic rows evaluated (forward-only, SDF+Jacobian)
 };
 

@@ -26,25 +26,6 @@ __global__ void k_latent_bias(DecoderDev dec, const float* __restrict__ codes, i
     }
 }
 
-// reference-shear / lattice voxel coordinates from the linear index (utils.py:97-116)
-__device__ __forceinline__ void grid_coord(int64_t i, int G, int coord_mode, float& x, float& y, float& z) {
-    const float vs = (float)(2.0 / (double)(G - 1));
-    const float Gf = (float)G;
-    const float zi = (float)(i % G);
-    float xi, yi;
-    if (coord_mode == 0) {
-        const float q = __fdiv_rn(__ll2float_rn(i), Gf);
-        yi = fmodf(q, Gf);
-        xi = fmodf(__fdiv_rn(q, Gf), Gf);
-    } else {
-        yi = (float)((i / G) % G);
-        xi = (float)((i / ((int64_t)G * G)) % G);
-    }
-    x = __fadd_rn(__fmul_rn(xi, vs), -1.f);
-    y = __fadd_rn(__fmul_rn(yi, vs), -1.f);
-    z = __fadd_rn(__fmul_rn(zi, vs), -1.f);
-}
-
 // ---------------------------------------------------------------------------
 // forward-only SDF of n rows with one code.  SRC 0: xyz array, SRC 1: voxel grid index
 // ---------------------------------------------------------------------------

@@ -1,10 +1,851 @@
-// placeholder until the tcgen05 kernels land (next commit): TC mode reports "unavailable"
+// tcgen05 decoder kernels of libdspslam_sm100 (DSPSLAM_MODE_TC).
+//
+// One persistent, warp-specialised kernel template evaluates the DeepSDF decoder
+// (deep_sdf/deep_sdf_decoder.py:75-110) - and, for the Jacobian variants, the input-gradient
+// sweep autograd performs for loss_utils.py:82-113 - on 128-row tiles:
+//
+//   * every 512-wide layer is a point x weight contraction on the 5th-generation tensor cores:
+//     D[128 x N] (FP32, TMEM) += A[128 x K] (FP16, shared memory) * W^T[K x N] (FP16, shared memory),
+//     issued by one thread as M128 x N<=128 x K16 `tcgen05.mma.cta_group::1.kind::f16`;
+//   * the weights are pre-packed on the host into 16 KB stage images that are already in the
+//     128-byte-swizzled K-major layout the MMA reads, and are streamed from L2 by a producer
+//     thread with 1-D bulk async copies (TMA) through a ring of mbarrier-guarded stages;
+//   * activations never leave the SM: the epilogue warps read the accumulators from TMEM
+//     (`tcgen05.ld`), apply ReLU while converting to FP16 and write the next layer's A operand
+//     straight into the swizzled shared-memory tile; ReLU sign bits are kept per thread for the
+//     backward sweep, which runs the transposed weight images through the same pipeline;
+//   * biases, the per-object latent contribution (c0/c4, see k_latent_bias) and the xyz columns
+//     of layers 0 and 4 enter as one extra K=16 MMA per layer: A_x = [1 1 x_hi x_lo ...],
+//     B_x = [b_hi b_lo W_hi W_hi W_lo ...] (hi/lo FP16 splits, so these terms keep ~FP32 accuracy);
+//   * the GN variants read their rows from the work lists built by the mode-independent kernels
+//     (kernels_simt.cu) and, for the Jacobian variant, reduce J^T J / J^T r per tile in shared memory.
 #include "kernels_tc.h"
+
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "tc_ptx.cuh"
+
 namespace dsp {
-int tc_pack_and_configure(DecoderDev&, const float* const*, const float* const*, __half**) { return 1; }
-const char* tc_last_error() { return "tcgen05 kernels not built"; }
-void tc_launch_sdf_rows(const DecoderDev&, int, const float*, int64_t, int64_t, int, int, const float*, const float*, float*, cudaStream_t) {}
-void tc_launch_sdf_jac(const DecoderDev&, int, const float*, int64_t, const float*, const float*, float*, float*, cudaStream_t) {}
-int tc_launch_gn_fwd(const GnWork&, int, cudaStream_t) { return 0; }
-int tc_launch_gn_jac(const GnWork&, int, cudaStream_t) { return 0; }
+namespace tc {
+
+using namespace ptx;
+
+constexpr int TILE_M = 128;
+constexpr int NT = 320;            // warps 0-7: epilogue, warp 8: weight producer, warp 9: MMA issuer
+constexpr int EPI_THREADS = 256;
+constexpr int A_BLK = 16384;       // one K=64 block of the activation tile: 128 rows x 128 B, SW128
+constexpr int A_BYTES = 8 * A_BLK;
+constexpr int AX_BYTES = 4096;     // the K=16 extra block of the tile: 128 rows x 32 B, no swizzle
+constexpr int STAGE_BYTES = 16384;
+constexpr int XTRA_BYTES = 16384;  // one extra-block B image: 512 rows x 32 B
+constexpr int JLD = 73;            // row stride (floats) of the per-row Jacobian buffer
+constexpr float GSCALE = 256.f;    // gradients are carried scaled so that FP16 keeps them normal
+constexpr int MAX_PROG = 256;
+constexpr int TMEM_COLS = 512;
+
+enum { ST_FIRST = 1, ST_BEGIN = 2, ST_END = 4, ST_OBJ = 8 };
+
+// One weight stage: what the producer copies and what the MMA thread issues for it.
+struct __align__(16) StageDesc {
+    uint32_t src;      // byte offset in the weight blob (ST_OBJ: inside the object's extras record)
+    uint16_t bytes16;  // bytes / 16
+    uint16_t dcol;     // first accumulator column
+    uint16_t n;        // B rows = accumulator columns covered by the stage
+    uint8_t kind;      // 0: SW128 K=64 block (4 MMAs of K=16), 1: K=16 extra block (N in chunks of 128)
+    uint8_t kb;        // activation K block (kind 0)
+    uint8_t flags;     // ST_*
+    uint8_t pad[3];
+};
+static_assert(sizeof(StageDesc) == 16, "StageDesc layout");
+
+__constant__ StageDesc c_fwd[MAX_PROG];
+__constant__ StageDesc c_bwd[MAX_PROG];
+__constant__ int c_nprog[2];
+
+struct TcArgs {
+    DecoderDev dec;
+    const uint8_t* blob;     // weight stage images
+    const uint8_t* xtra;     // per-object extras: [obj][2][XTRA_BYTES] (layer 0, layer 4)
+    // stand-alone row sources / sinks
+    const float* xyz;
+    int64_t n, i0;
+    int G;
+    float* out;
+    float* jac_out;
+    int n_tiles;
+    // Gauss-Newton work lists
+    GnWork w;
+};
+
+template <int MODE>
+struct Cfg {
+    static constexpr bool JAC = MODE >= 4;
+    static constexpr bool GN = (MODE == 3 || MODE == 5);
+    static constexpr int NST = JAC ? 3 : 5;
+    static constexpr int O_AX = A_BYTES;
+    static constexpr int O_ST = O_AX + AX_BYTES;
+    static constexpr int O_W8 = O_ST + NST * STAGE_BYTES;
+    static constexpr int O_XYZ = O_W8 + 2048;
+    static constexpr int O_PART = O_XYZ + 2048;
+    static constexpr int O_DY = O_PART + 1024;
+    static constexpr int O_BAR = O_DY + 512;
+    static constexpr int O_JROW = O_BAR + 256;
+    static constexpr int O_WROW = O_JROW + (JAC ? TILE_M * JLD * 4 : 0);
+    static constexpr int O_RT = O_WROW + (JAC ? 512 : 0);
+    static constexpr int O_END = O_RT + (JAC ? 512 : 0);
+    static constexpr int SMEM = O_END + 1024;   // + alignment slack
+};
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
+
+__device__ __forceinline__ void split_f16(float v, __half& hi, __half& lo) {
+    hi = __float2half_rn(v);
+    lo = __float2half_rn(v - __half2float(hi));
+}
+
+__device__ __forceinline__ void build_pose_row(float* J, float gx, float gy, float gz, float x, float y, float z) {
+    // d x_o / d xi = [I | -hat(x) | x]  (loss_utils.py:176-195)
+    J[0] = gx; J[1] = gy; J[2] = gz;
+    J[3] = y * gz - z * gy;
+    J[4] = z * gx - x * gz;
+    J[5] = x * gy - y * gx;
+    J[6] = gx * x + gy * y + gz * z;
+}
+
+// MODE 0: rows = xyz array -> out            1: voxel grid, reference shear -> out   2: voxel grid, lattice -> out
+//      3: GN forward (compacted ray samples) 4: xyz array -> sdf + jac               5: GN Jacobian rows -> J^T J partials
+template <int MODE>
+__global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) {
+    using C = Cfg<MODE>;
+    constexpr bool JAC = C::JAC;
+    constexpr int NST = C::NST;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase = (raw + 1023u) & ~1023u;
+    uint8_t* sm = smem_raw + (sbase - raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    const uint32_t sA = sbase, sAX = sbase + C::O_AX, sST = sbase + C::O_ST;
+    float* w8s = reinterpret_cast<float*>(sm + C::O_W8);
+    float4* xyzs = reinterpret_cast<float4*>(sm + C::O_XYZ);
+    float* parts = reinterpret_cast<float*>(sm + C::O_PART);
+    float* dys = reinterpret_cast<float*>(sm + C::O_DY);
+    const uint32_t bar0 = sbase + C::O_BAR;
+    auto bar_full = [&](int s) { return bar0 + 8u * s; };
+    auto bar_empty = [&](int s) { return bar0 + 8u * (NST + s); };
+    const uint32_t bar_aready = bar0 + 8u * (2 * NST), bar_dfull = bar0 + 8u * (2 * NST + 1);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + C::O_BAR + 8 * (2 * NST + 2));
+    float* jrow = reinterpret_cast<float*>(sm + C::O_JROW);
+    float* wrows = reinterpret_cast<float*>(sm + C::O_WROW);
+    float* rts = reinterpret_cast<float*>(sm + C::O_RT);
+
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+        mbar_init(bar_aready, 8);
+        mbar_init(bar_dfull, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) {
+        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+        tmem_relinquish();
+    }
+    for (int i = tid; i < HID; i += NT) w8s[i] = __ldg(a.dec.w8 + i);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+
+    int n_tiles = a.n_tiles;
+    if (C::GN) n_tiles = a.w.n_tiles[MODE == 3 ? 0 : 1];
+    constexpr int NPROG = JAC ? 2 : 1;
+
+    if (warp == 8) {
+        // ===================== weight producer (one thread) =====================
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                const int obj = C::GN ? a.w.tile_obj[t] : 0;
+                const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
+                for (int p = 0; p < NPROG; ++p) {
+                    const StageDesc* prog = p ? c_bwd : c_fwd;
+                    const int np = c_nprog[p];
+                    for (int e = 0; e < np; ++e) {
+                        const StageDesc d = prog[e];
+                        mbar_wait(bar_empty(s), ph ^ 1u);
+                        const uint32_t bytes = (uint32_t)d.bytes16 * 16u;
+                        mbar_expect_tx(bar_full(s), bytes);
+                        const uint8_t* src = (d.flags & ST_OBJ) ? xo + d.src : a.blob + d.src;
+                        bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                        if (++s == NST) { s = 0; ph ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer (one thread) =====================
+        if (lane == 0) {
+            uint32_t s = 0, ph = 0, aph = 0;
+            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+                for (int p = 0; p < NPROG; ++p) {
+                    const StageDesc* prog = p ? c_bwd : c_fwd;
+                    const int np = c_nprog[p];
+                    for (int e = 0; e < np; ++e) {
+                        const StageDesc d = prog[e];
+                        if (d.flags & ST_BEGIN) {           // activations of this layer written, accumulator drained
+                            mbar_wait(bar_aready, aph);
+                            aph ^= 1u;
+                        }
+                        mbar_wait(bar_full(s), ph);
+                        tc_fence_after();
+                        const uint32_t sB = sST + s * STAGE_BYTES;
+                        if (d.kind == 0) {
+                            const uint32_t id = idesc_f16(TILE_M, d.n);
+                            const uint32_t a0 = sA + (uint32_t)d.kb * A_BLK;
+#pragma unroll
+                            for (int ks = 0; ks < 4; ++ks)
+                                umma_f16(tmem + d.dcol, smem_desc(a0 + ks * 32, 16, 1024, 2),
+                                         smem_desc(sB + ks * 32, 16, 1024, 2), id,
+                                         ((d.flags & ST_FIRST) && ks == 0) ? 0u : 1u);
+                        } else {
+                            const uint64_t ad = smem_desc(sAX, 128, 256, 0);
+                            for (int n0 = 0; n0 < d.n; n0 += 128) {
+                                const int nn = min(128, (int)d.n - n0);
+                                umma_f16(tmem + d.dcol + n0, ad, smem_desc(sB + n0 * 32, 128, 256, 0),
+                                         idesc_f16(TILE_M, nn), (d.flags & ST_FIRST) ? 0u : 1u);
+                            }
+                        }
+                        umma_commit(bar_empty(s));                       // stage reusable once these MMAs finish
+                        if (d.flags & ST_END) umma_commit(bar_dfull);    // accumulator of the layer complete
+                        if (++s == NST) { s = 0; ph ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int q = warp & 3, hc = warp >> 2;
+        const int r = q * 32 + lane;                       // tile row = TMEM lane
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        const int rx = r & 7;
+        const uint32_t a_row = sA + (uint32_t)(r >> 3) * 1024u + (uint32_t)rx * 128u;
+        const int etid = tid;                              // 0..255
+        uint32_t dph = 0;
+        uint32_t mw[8][8];                                 // ReLU sign words of this thread's 256 columns, per layer
+        const int L = a.dec.L;
+
+        auto signal_ready = [&]() {
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_aready);
+        };
+        // write 32 consecutive FP16 values (16 packed words) of row r at column `col` of the activation tile
+        auto store32 = [&](int col, const uint32_t* p) {
+            const uint32_t blk = a_row + (uint32_t)(col >> 6) * A_BLK;
+            const int cc0 = (col & 63) >> 3;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq)
+                st_shared_v4(blk + (uint32_t)(((cc0 + qq) ^ rx) << 4), p[4 * qq], p[4 * qq + 1], p[4 * qq + 2], p[4 * qq + 3]);
+        };
+
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            // ---------------- tile rows ----------------
+            int obj = 0, row0 = 0, rows_valid = 0;
+            int dest = -1;
+            bool valid = false;
+            float coef = 0.f, resid = 0.f;
+            int M_obj = 0;
+            size_t jb = 0;
+            if (MODE == 3) {
+                obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
+                rows_valid = min(TILE_M, a.w.st[obj].n_valid - row0);
+            } else if (MODE == 5) {
+                obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
+                M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
+                const int K = a.w.prm.pose_only ? 0 : a.w.st[obj].K;
+                rows_valid = min(TILE_M, M_obj + K - row0);
+                jb = (size_t)a.w.pts_off[obj] + (size_t)a.w.ray_off[obj] * a.w.prm.D;
+            } else {
+                const int64_t left = a.n - (int64_t)t * TILE_M;
+                rows_valid = (int)(left < TILE_M ? left : TILE_M);
+            }
+            if (hc == 0) {
+                float x = 0.f, y = 0.f, z = 0.f;
+                valid = r < rows_valid;
+                if (valid) {
+                    if (MODE == 0 || MODE == 4) {
+                        const int64_t gr = (int64_t)t * TILE_M + r;
+                        x = a.xyz[gr * 3 + 0]; y = a.xyz[gr * 3 + 1]; z = a.xyz[gr * 3 + 2];
+                    } else if (MODE == 1 || MODE == 2) {
+                        grid_coord(a.i0 + (int64_t)t * TILE_M + r, a.G, MODE - 1, x, y, z);
+                    } else if (MODE == 3) {
+                        const float4 v = a.w.frows[(size_t)a.w.ray_off[obj] * a.w.prm.D + row0 + r];
+                        x = v.x; y = v.y; z = v.z; dest = __float_as_int(v.w);
+                    } else {
+                        const float4 v = a.w.jrows[jb + row0 + r];
+                        x = v.x; y = v.y; z = v.z; coef = v.w;
+                        if (row0 + r >= M_obj) resid = a.w.jres[jb + row0 + r];
+                    }
+                }
+                xyzs[r] = make_float4(x, y, z, coef);
+                __half xh, xl, yh, yl, zh, zl;
+                split_f16(x, xh, xl); split_f16(y, yh, yl); split_f16(z, zh, zl);
+                const __half one = __float2half_rn(1.f), zero = __float2half_rn(0.f);
+                const __half2 c0a = __halves2half2(one, one), c0b = __halves2half2(xh, yh), c0c = __halves2half2(zh, xl),
+                              c0d = __halves2half2(yl, zl);
+                const __half2 c1a = __halves2half2(xh, yh), c1b = __halves2half2(zh, zero), c1z = __halves2half2(zero, zero);
+                const uint32_t ax = sAX + (uint32_t)(r >> 3) * 256u + (uint32_t)rx * 16u;
+                st_shared_v4(ax, *reinterpret_cast<const uint32_t*>(&c0a), *reinterpret_cast<const uint32_t*>(&c0b),
+                             *reinterpret_cast<const uint32_t*>(&c0c), *reinterpret_cast<const uint32_t*>(&c0d));
+                st_shared_v4(ax + 128u, *reinterpret_cast<const uint32_t*>(&c1a), *reinterpret_cast<const uint32_t*>(&c1b),
+                             *reinterpret_cast<const uint32_t*>(&c1z), *reinterpret_cast<const uint32_t*>(&c1z));
+            }
+            signal_ready();                                 // layer 0 may start (A_x written, accumulator free)
+
+            // ---------------- forward ----------------
+            float sdf_y = 0.f;
+            for (int l = 0; l < 8; ++l) {
+                const bool last = (l == 7);
+                const int ncols = (l == 3) ? a.dec.h3p : HID;
+                mbar_wait(bar_dfull, dph);
+                dph ^= 1u;
+                tc_fence_after();
+                float part = 0.f;
+#pragma unroll 1
+                for (int jp = 0; jp < 4; ++jp) {
+                    const int col = hc * 256 + jp * 64;
+                    if (col >= ncols) {
+                        if (JAC) { mw[l][2 * jp] = 0u; mw[l][2 * jp + 1] = 0u; }
+                        continue;
+                    }
+                    uint32_t v0[32], v1[32];
+                    tmem_ld32(trow + col, v0);
+                    tmem_ld32(trow + col + 32, v1);
+                    tmem_ld_wait();
+                    if (JAC) {
+                        uint32_t m0 = 0u, m1 = 0u;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            m0 = __funnelshift_l(v0[i], m0, 1);
+                            m1 = __funnelshift_l(v1[i], m1, 1);
+                        }
+                        mw[l][2 * jp] = ~m0;                 // bit (31-i) set <=> pre-activation i positive
+                        mw[l][2 * jp + 1] = ~m1;
+                    }
+                    if (!last) {
+                        uint32_t p[16];
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            p[i] = pack_relu_f16x2(__uint_as_float(v0[2 * i]), __uint_as_float(v0[2 * i + 1]));
+                        store32(col, p);
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            p[i] = pack_relu_f16x2(__uint_as_float(v1[2 * i]), __uint_as_float(v1[2 * i + 1]));
+                        store32(col + 32, p);
+                    } else {                                  // layer 8 (1 x 512) folded into the last epilogue
+                        const float4* w4 = reinterpret_cast<const float4*>(w8s + col);
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const float4 wa = w4[i], wb = w4[8 + i];
+                            part = fmaf(fmaxf(__uint_as_float(v0[4 * i + 0]), 0.f), wa.x, part);
+                            part = fmaf(fmaxf(__uint_as_float(v0[4 * i + 1]), 0.f), wa.y, part);
+                            part = fmaf(fmaxf(__uint_as_float(v0[4 * i + 2]), 0.f), wa.z, part);
+                            part = fmaf(fmaxf(__uint_as_float(v0[4 * i + 3]), 0.f), wa.w, part);
+                            part = fmaf(fmaxf(__uint_as_float(v1[4 * i + 0]), 0.f), wb.x, part);
+                            part = fmaf(fmaxf(__uint_as_float(v1[4 * i + 1]), 0.f), wb.y, part);
+                            part = fmaf(fmaxf(__uint_as_float(v1[4 * i + 2]), 0.f), wb.z, part);
+                            part = fmaf(fmaxf(__uint_as_float(v1[4 * i + 3]), 0.f), wb.w, part);
+                        }
+                    }
+                }
+                if (!last) {
+                    signal_ready();
+                } else {
+                    parts[hc * TILE_M + r] = part;
+                    tc_fence_before();
+                    named_bar_sync(1, EPI_THREADS);
+                    sdf_y = tanhf(parts[r] + parts[TILE_M + r] + a.dec.b8);
+                }
+            }
+
+            if (!JAC) {
+                if (hc == 0 && valid) {
+                    if (MODE == 3) a.w.sdf_samp[dest] = sdf_y;
+                    else a.out[(int64_t)t * TILE_M + r] = sdf_y;
+                }
+                named_bar_sync(1, EPI_THREADS);             // `parts` reusable
+                continue;
+            }
+
+            // ---------------- backward (input-gradient sweep) ----------------
+            if (JAC) {
+                const float dyS = GSCALE * (1.f - sdf_y * sdf_y);
+                // g7 = dy * w8 . relu'(a7)
+#pragma unroll 1
+                for (int j = 0; j < 8; ++j) {
+                    const int col = hc * 256 + j * 32;
+                    const uint32_t m = mw[7][j];
+                    const float4* w4 = reinterpret_cast<const float4*>(w8s + col);
+                    uint32_t p[16];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 wv = w4[i];
+                        const float e0 = ((m << (4 * i + 0)) & 0x80000000u) ? dyS * wv.x : 0.f;
+                        const float e1 = ((m << (4 * i + 1)) & 0x80000000u) ? dyS * wv.y : 0.f;
+                        const float e2 = ((m << (4 * i + 2)) & 0x80000000u) ? dyS * wv.z : 0.f;
+                        const float e3 = ((m << (4 * i + 3)) & 0x80000000u) ? dyS * wv.w : 0.f;
+                        p[2 * i] = pack_f16x2(e0, e1);
+                        p[2 * i + 1] = pack_f16x2(e2, e3);
+                    }
+                    store32(col, p);
+                }
+                signal_ready();
+
+                // steps l = 7..1: D = g_l W_l  -> mask with relu'(a_{l-1}) -> next A
+                for (int l = 7; l >= 1; --l) {
+                    mbar_wait(bar_dfull, dph);
+                    dph ^= 1u;
+                    tc_fence_after();
+                    const bool split = (l == 4);             // columns >= h3 are d/d(input) (latent re-injection)
+                    const int h3 = a.dec.h3, h3p = a.dec.h3p;
+#pragma unroll 1
+                    for (int j = 0; j < 8; ++j) {
+                        const int col = hc * 256 + j * 32;
+                        uint32_t v[32];
+                        tmem_ld32(trow + col, v);
+                        tmem_ld_wait();
+                        const uint32_t m = mw[l - 1][j];
+                        if (split && col >= h3p) {           // pure input-gradient columns
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) jrow[r * JLD + (col + i - h3)] = __uint_as_float(v[i]);
+                            continue;
+                        }
+                        uint32_t p[16];
+                        if (split && col + 32 > h3) {        // the group that straddles h3 (445)
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                const bool hid = (col + i) < h3;
+                                if (!hid) jrow[r * JLD + (col + i - h3)] = __uint_as_float(v[i]);
+                                if (!hid || !((m << i) & 0x80000000u)) v[i] = 0u;
+                            }
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (!((m << i) & 0x80000000u)) v[i] = 0u;
+                        }
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            p[i] = pack_f16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+                        store32(col, p);
+                    }
+                    signal_ready();
+                }
+
+                // step l = 0: D[:, 0..in_dim) = g_0 W_0 ;  jac = (D + gin) / GSCALE
+                mbar_wait(bar_dfull, dph);
+                dph ^= 1u;
+                tc_fence_after();
+                const float inv_s = 1.f / GSCALE;
+                if (hc == 0) {
+                    uint32_t v0[32], v1[32], v2[32];
+                    tmem_ld32(trow + 0, v0);
+                    tmem_ld32(trow + 32, v1);
+                    tmem_ld32(trow + 64, v2);
+                    tmem_ld_wait();
+                    float* jr = jrow + r * JLD;
+                    if (MODE == 4) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            if (i < L + 3) jr[i] = (__uint_as_float(v0[i]) + jr[i]) * inv_s;
+                            if (32 + i < L + 3) jr[32 + i] = (__uint_as_float(v1[i]) + jr[32 + i]) * inv_s;
+                            if (64 + i < L + 3) jr[64 + i] = (__uint_as_float(v2[i]) + jr[64 + i]) * inv_s;
+                        }
+                    } else {
+                        // J row = [pose 7 | code L] in place over gin: read the xyz part first, then descend
+                        auto dval = [&](int i) -> float {
+                            return __uint_as_float(i < 32 ? v0[i & 31] : (i < 64 ? v1[i & 31] : v2[i & 31]));
+                        };
+                        float gxyz[3];
+#pragma unroll
+                        for (int c = 0; c < 3; ++c) gxyz[c] = 0.f;
+#pragma unroll
+                        for (int i = 0; i < 96; ++i) {
+                            if (i >= L && i < L + 3) gxyz[i - L] = (dval(i) + jr[i]) * inv_s;
+                        }
+                        const float4 pc = xyzs[r];
+                        const float cf = pc.w;
+#pragma unroll
+                        for (int i = 95; i >= 0; --i) {
+                            if (i < L) jr[POSE + i] = cf * (dval(i) + jr[i]) * inv_s;
+                        }
+                        build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
+                    }
+                }
+                tc_fence_before();
+
+                if (MODE == 4) {
+                    named_bar_sync(1, EPI_THREADS);
+                    const int in_dim = L + 3;
+                    const int64_t g0 = (int64_t)t * TILE_M;
+                    if (hc == 0 && valid) a.out[g0 + r] = sdf_y;
+                    for (int e = etid; e < rows_valid * in_dim; e += EPI_THREADS) {
+                        const int row = e / in_dim, i = e - row * in_dim;
+                        a.jac_out[(g0 + row) * in_dim + i] = jrow[row * JLD + i];
+                    }
+                    named_bar_sync(1, EPI_THREADS);
+                } else {
+                    // ---- residual weights, then J^T J / J^T r of the tile (optimizer.py:163-169) ----
+                    const GnWork& w = a.w;
+                    const ObjState& so = w.st[obj];
+                    const int K = w.prm.pose_only ? 0 : so.K;
+                    const float w_s = (w.prm.pose_only ? 1.f : w.prm.k2) / (float)so.M_active;
+                    const float w_r = w.prm.k1 / (float)K;
+                    float ls = 0.f, lr = 0.f;
+                    if (hc == 0) {
+                        float wr = 0.f, rt = 0.f;
+                        if (valid) {
+                            const int rr = row0 + r;
+                            if (rr < M_obj) {                                 // surface row: residual = SDF itself
+                                w.sres[w.pts_off[obj] + rr] = sdf_y;
+                                rt = w.prm.pose_only ? sdf_y : huber_res(sdf_y, w.prm.b2);
+                                if (coef != 0.f) { wr = w_s; ls = rt * rt; }
+                            } else {                                          // render row
+                                rt = huber_res(resid, w.prm.b1);
+                                wr = w_r;
+                                lr = rt * rt;
+                            }
+                        }
+                        wrows[r] = wr;
+                        rts[r] = rt;
+                    }
+                    named_bar_sync(1, EPI_THREADS);
+                    const int n = POSE + L;
+                    constexpr int NQ = (HMAX * HMAX + HMAX + EPI_THREADS - 1) / EPI_THREADS;   // 20
+                    float acc[NQ];
+#pragma unroll
+                    for (int qn = 0; qn < NQ; ++qn) {
+                        const int e = etid + qn * EPI_THREADS;
+                        float s = 0.f;
+                        if (e < n * n) {
+                            const int i = e / n, j = e - i * n;
+                            for (int row = 0; row < TILE_M; ++row)
+                                s = fmaf(wrows[row] * jrow[row * JLD + i], jrow[row * JLD + j], s);
+                        } else if (e < n * n + n) {
+                            const int i = e - n * n;
+                            for (int row = 0; row < TILE_M; ++row)
+                                s = fmaf(-wrows[row] * jrow[row * JLD + i], rts[row], s);
+                        }
+                        acc[qn] = s;
+                    }
+                    float* part = w.partials + ((size_t)obj * w.jgroups_max + (row0 / GROUP_ROWS)) * PART_STRIDE;
+#pragma unroll
+                    for (int qn = 0; qn < NQ; ++qn) {
+                        const int e = etid + qn * EPI_THREADS;
+                        if (e < n * n + n) part[e] = acc[qn];
+                    }
+                    if (hc == 0) {                                           // loss sums over the 128 rows
+                        for (int o = 16; o > 0; o >>= 1) {
+                            ls += __shfl_xor_sync(0xffffffffu, ls, o);
+                            lr += __shfl_xor_sync(0xffffffffu, lr, o);
+                        }
+                        if (lane == 0) { parts[q] = ls; parts[4 + q] = lr; }
+                    }
+                    named_bar_sync(1, EPI_THREADS);
+                    if (etid == 0) {
+                        part[PART_LOSS] = parts[0] + parts[1] + parts[2] + parts[3];
+                        part[PART_LOSS + 1] = parts[4] + parts[5] + parts[6] + parts[7];
+                    }
+                    named_bar_sync(1, EPI_THREADS);
+                }
+            }
+        }
+    }
+
+    // ---------------- teardown ----------------
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-object extra blocks of layers 0 and 4 (B operand of the K=16 MMA):
+//   k=0,1: hi/lo of the latent bias c (k_latent_bias / k_gn_prep);  k=2..4: hi(W_xyz) (x x_hi);
+//   k=5..7: hi(W_xyz) (x x_lo);  k=8..10: lo(W_xyz) (x x_hi)
+// image layout (no swizzle, K-major): byte(n, k) = (n/8)*256 + (k/8)*128 + (n%8)*16 + (k%8)*2
+// ------------------------------------------------------------------------------------------------
+__global__ void k_tc_pack_extra(DecoderDev dec, const float* __restrict__ c0, const float* __restrict__ c4,
+                                const int* __restrict__ status, int stride_st, uint8_t* __restrict__ xtra) {
+    const int b = blockIdx.x, which = blockIdx.y, n = threadIdx.x;
+    if (status && *reinterpret_cast<const int*>(reinterpret_cast<const char*>(status) + (size_t)b * stride_st) != 0) return;
+    const float bias = which ? c4[(size_t)b * HID + n] : c0[(size_t)b * HID + n];
+    float wx[3];
+    for (int c = 0; c < 3; ++c)
+        wx[c] = which ? __ldg(dec.W4in + (size_t)(dec.L + c) * HID + n) : __ldg(dec.W0x4 + (size_t)c * HID + n);
+    __half h[16];
+    for (int k = 0; k < 16; ++k) h[k] = __float2half_rn(0.f);
+    split_f16(bias, h[0], h[1]);
+    for (int c = 0; c < 3; ++c) {
+        __half hi, lo;
+        split_f16(wx[c], hi, lo);
+        h[2 + c] = hi; h[5 + c] = hi; h[8 + c] = lo;
+    }
+    uint8_t* dst = xtra + ((size_t)b * 2 + which) * XTRA_BYTES + (size_t)(n >> 3) * 256 + (size_t)(n & 7) * 16;
+    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(&h[0]);
+    *reinterpret_cast<uint4*>(dst + 128) = *reinterpret_cast<const uint4*>(&h[8]);
+}
+
+// work lists of the GN kernels: 128-row tiles per object (objects that failed get none)
+__global__ void k_tc_plan(GnWork w, int which) {
+    __shared__ int s_scan[1024];
+    __shared__ int s_carry;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < w.B; base += blockDim.x) {
+        const int b = base + tid;
+        int nt = 0, rows = 0;
+        if (b < w.B && w.st[b].status == 0) {
+            if (which == 0) rows = w.st[b].n_valid;
+            else rows = (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : w.st[b].K);
+            nt = (rows + TILE_M - 1) / TILE_M;
+        }
+        s_scan[tid] = nt;
+        __syncthreads();
+        for (int o = 1; o < (int)blockDim.x; o <<= 1) {           // Hillis-Steele inclusive scan
+            int v = (tid >= o) ? s_scan[tid - o] : 0;
+            __syncthreads();
+            s_scan[tid] += v;
+            __syncthreads();
+        }
+        const int first = s_carry + s_scan[tid] - nt;
+        for (int i = 0; i < nt; ++i) { w.tile_obj[first + i] = b; w.tile_row0[first + i] = i * TILE_M; }
+        __syncthreads();
+        if (tid == (int)blockDim.x - 1) s_carry += s_scan[tid];
+        __syncthreads();
+    }
+    if (tid == 0) w.n_tiles[which] = s_carry;
+}
+
+}  // namespace tc
+
+// ------------------------------------------------------------------------------------------------
+// host side: weight packing, program tables, launchers
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+std::string g_tc_err;
+
+struct BlobBuilder {
+    std::vector<uint8_t> bytes;
+    std::vector<tc::StageDesc> prog[2];
+
+    size_t alloc(size_t n) {
+        const size_t at = (bytes.size() + 127) & ~(size_t)127;
+        bytes.resize(at + n, 0);
+        return at;
+    }
+    static uint16_t f2h(float v) {
+        __half h = __float2half_rn(v);
+        uint16_t u;
+        memcpy(&u, &h, 2);
+        return u;
+    }
+    static float h2f(uint16_t u) {
+        __half h;
+        memcpy(&h, &u, 2);
+        return __half2float(h);
+    }
+    // SW128 K-major image of rows [n0, n0+nn) x k in [kb*64, kb*64+64) of the matrix elem(row, k)
+    template <class F>
+    size_t sw128(int n0, int nn, int kb, F elem) {
+        const size_t at = alloc((size_t)nn * 128);
+        for (int rr = 0; rr < nn; ++rr)
+            for (int k = 0; k < 64; ++k) {
+                const size_t off = (size_t)(rr >> 3) * 1024 + (size_t)(rr & 7) * 128 + (size_t)(((k >> 3) ^ (rr & 7)) << 4) + (size_t)(k & 7) * 2;
+                const uint16_t h = f2h(elem(n0 + rr, kb * 64 + k));
+                memcpy(&bytes[at + off], &h, 2);
+            }
+        return at;
+    }
+};
+
+}  // namespace
+
+const char* tc_last_error() { return g_tc_err.c_str(); }
+
+size_t tc_xtra_bytes_per_object() { return 2 * (size_t)tc::XTRA_BYTES; }
+
+int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* const* b, __half** hblob) {
+    using namespace tc;
+    const int h3 = dec.h3, h3p = dec.h3p, in_dim = dec.in_dim;
+    if (h3p % 64 != 0) {          // the K blocks are 64 wide; code_len 64 gives 448
+        g_tc_err = "tcgen05 path needs (512 - code_len - 3) rounded up to 16 to be a multiple of 64 (code_len 64)";
+        return 1;
+    }
+    BlobBuilder B;
+    auto push = [&](int p, size_t src, size_t bytes, int dcol, int n, int kind, int kb, int flags) {
+        StageDesc d{};
+        d.src = (uint32_t)src; d.bytes16 = (uint16_t)(bytes / 16); d.dcol = (uint16_t)dcol; d.n = (uint16_t)n;
+        d.kind = (uint8_t)kind; d.kb = (uint8_t)kb; d.flags = (uint8_t)flags;
+        B.prog[p].push_back(d);
+    };
+    // ---- forward program ----
+    push(0, 0, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_END | ST_OBJ);            // layer 0: extras only
+    for (int l = 1; l < 8; ++l) {
+        const int N = (l == 3) ? h3p : HID, K = (l == 4) ? h3p : HID;
+        const int Nreal = (l == 3) ? h3 : HID, Kreal = (l == 4) ? h3 : HID;
+        if (l == 4) {
+            push(0, XTRA_BYTES, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_OBJ);
+        } else {                                                                           // static bias block
+            const size_t at = B.alloc((size_t)N * 32);
+            for (int n = 0; n < Nreal; ++n) {
+                const uint16_t hi = BlobBuilder::f2h(b[l][n]);
+                const uint16_t lo = BlobBuilder::f2h(b[l][n] - BlobBuilder::h2f(hi));
+                const size_t off = at + (size_t)(n >> 3) * 256 + (size_t)(n & 7) * 16;
+                memcpy(&B.bytes[off], &hi, 2);
+                memcpy(&B.bytes[off + 2], &lo, 2);
+            }
+            push(0, at, (size_t)N * 32, 0, N, 1, 0, ST_FIRST | ST_BEGIN);
+        }
+        const float* Wl = W[l];
+        for (int n0 = 0; n0 < N; n0 += 128) {
+            const int nn = std::min(128, N - n0);
+            for (int kb = 0; kb < K / 64; ++kb) {
+                const size_t at = B.sw128(n0, nn, kb, [&](int n, int k) -> float {
+                    return (n < Nreal && k < Kreal) ? Wl[(size_t)n * HID + k] : 0.f;        // W[l] is [out][512]
+                });
+                const bool end = (n0 + nn == N) && (kb == K / 64 - 1);
+                push(0, at, (size_t)nn * 128, n0, nn, 0, kb, end ? ST_END : 0);
+            }
+        }
+    }
+    // ---- backward program: D[:, i] = sum_o g[:, o] W_l[o][i] ----
+    for (int l = 7; l >= 1; --l) {
+        const int K = (l == 3) ? h3p : HID, Kreal = (l == 3) ? h3 : HID;                   // outputs of layer l
+        const float* Wl = W[l];
+        for (int n0 = 0; n0 < HID; n0 += 128) {
+            for (int kb = 0; kb < K / 64; ++kb) {
+                const size_t at = B.sw128(n0, 128, kb, [&](int i, int o) -> float {
+                    return (o < Kreal) ? Wl[(size_t)o * HID + i] : 0.f;
+                });
+                int fl = 0;
+                if (kb == 0) fl |= ST_FIRST;
+                if (n0 == 0 && kb == 0) fl |= ST_BEGIN;
+                if (n0 == HID - 128 && kb == K / 64 - 1) fl |= ST_END;
+                push(1, at, 128 * 128, n0, 128, 0, kb, fl);
+            }
+        }
+    }
+    {
+        const int N0 = (in_dim + 15) & ~15;                                                // 80
+        for (int kb = 0; kb < HID / 64; ++kb) {
+            const size_t at = B.sw128(0, N0, kb, [&](int i, int o) -> float {
+                return (i < in_dim) ? W[0][(size_t)o * in_dim + i] : 0.f;
+            });
+            int fl = 0;
+            if (kb == 0) fl |= ST_FIRST | ST_BEGIN;
+            if (kb == HID / 64 - 1) fl |= ST_END;
+            push(1, at, (size_t)N0 * 128, 0, N0, 0, kb, fl);
+        }
+    }
+    if (B.prog[0].size() > MAX_PROG || B.prog[1].size() > MAX_PROG) { g_tc_err = "stage program too long"; return 2; }
+
+    // device: [weight images | one extras record for the single-code entry points]
+    const size_t wbytes = (B.bytes.size() + 255) & ~(size_t)255;
+    const size_t total = wbytes + 2 * XTRA_BYTES;
+    uint8_t* dev = nullptr;
+    cudaError_t e = cudaMalloc(&dev, total);
+    if (e != cudaSuccess) { g_tc_err = cudaGetErrorString(e); return 2; }
+    e = cudaMemcpy(dev, B.bytes.data(), B.bytes.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(dev + wbytes, 0, 2 * XTRA_BYTES);
+    const int np[2] = {(int)B.prog[0].size(), (int)B.prog[1].size()};
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd, B.prog[0].data(), sizeof(StageDesc) * np[0]);
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd, B.prog[1].data(), sizeof(StageDesc) * np[1]);
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_nprog, np, sizeof(np));
+#define TC_ATTR(MODE)                                                                                          \
+    if (e == cudaSuccess)                                                                                      \
+        e = cudaFuncSetAttribute(k_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<MODE>::SMEM);
+    TC_ATTR(0) TC_ATTR(1) TC_ATTR(2) TC_ATTR(3) TC_ATTR(4) TC_ATTR(5)
+#undef TC_ATTR
+    if (e != cudaSuccess) {
+        g_tc_err = cudaGetErrorString(e);
+        cudaFree(dev);
+        return 2;
+    }
+    *hblob = reinterpret_cast<__half*>(dev);
+    dec.tc_blob = dev;
+    dec.tc_xtra1 = dev + wbytes;
+    return 0;
+}
+
+namespace {
+template <int MODE>
+void launch_tc(const tc::TcArgs& a, int grid, cudaStream_t st) {
+    tc::k_tc<MODE><<<grid, tc::NT, tc::Cfg<MODE>::SMEM, st>>>(a);
+}
+}  // namespace
+
+int tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, int64_t i0, int G,
+                       int src_mode, const float* c0, const float* c4, float* out, cudaStream_t st) {
+    using namespace tc;
+    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, nullptr, 0, dec.tc_xtra1);
+    TcArgs a{};
+    a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
+    a.xyz = xyz; a.n = n; a.i0 = i0; a.G = G; a.out = out;
+    a.n_tiles = (int)((n + TILE_M - 1) / TILE_M);
+    const int grid = std::min(a.n_tiles, sm_count);
+    if (src_mode == 0) launch_tc<0>(a, grid, st);
+    else if (src_mode == 1) launch_tc<1>(a, grid, st);
+    else launch_tc<2>(a, grid, st);
+    return 2;
+}
+
+int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
+                      const float* c4, float* sdf_out, float* jac_out, cudaStream_t st) {
+    using namespace tc;
+    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, nullptr, 0, dec.tc_xtra1);
+    TcArgs a{};
+    a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
+    a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
+    a.n_tiles = (int)((n + TILE_M - 1) / TILE_M);
+    launch_tc<4>(a, std::min(a.n_tiles, sm_count), st);
+    return 2;
+}
+
+// per-object extras are packed once per iteration (by the forward launch, or by the Jacobian launch in
+// the ray-less pose-only driver)
+static void pack_extras_gn(const GnWork& w, cudaStream_t st) {
+    tc::k_tc_pack_extra<<<dim3(w.B, 2), HID, 0, st>>>(w.dec, w.c0, w.c4, &w.st[0].status, (int)sizeof(ObjState),
+                                                      w.tc_xtra);
+}
+
+int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st) {
+    using namespace tc;
+    pack_extras_gn(w, st);
+    k_tc_plan<<<1, 1024, 0, st>>>(w, 0);
+    TcArgs a{};
+    a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
+    launch_tc<3>(a, sm_count, st);
+    return 3;
+}
+
+int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {
+    using namespace tc;
+    int nl = 2;
+    if (w.prm.pose_only) { pack_extras_gn(w, st); ++nl; }
+    k_tc_plan<<<1, 1024, 0, st>>>(w, 1);
+    TcArgs a{};
+    a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
+    launch_tc<5>(a, sm_count, st);
+    return nl;
+}
+
+}  // namespace dsp
