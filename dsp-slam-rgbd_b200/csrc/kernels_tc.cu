@@ -6,9 +6,9 @@
 //
 //   * every 512-wide layer is a point x weight contraction on the 5th-generation tensor cores:
 //     D[128 x N] (FP32, TMEM) += A[128 x K] (FP16, shared memory) * W^T[K x N] (FP16, shared memory),
-//     issued by one thread as M128 x N<=128 x K16 `tcgen05.mma.cta_group::1.kind::f16`;
-//   * the weights are pre-packed on the host into 16 KB stage images that are already in the
-//     128-byte-swizzled K-major layout the MMA reads, and are streamed from L2 by a producer
+//     issued by one thread as M128 x N<=256 x K16 `tcgen05.mma.cta_group::1.kind::f16`;
+//   * the weights are pre-packed on the host into 16 KB stage images (256 outputs x 32 K values) that are
+//     already in the 64-byte-swizzled K-major layout the MMA reads, and are streamed from L2 by a producer
 //     thread with 1-D bulk async copies (TMA) through a ring of mbarrier-guarded stages;
 //   * activations never leave the SM: the epilogue warps read the accumulators from TMEM
 //     (`tcgen05.ld`), apply ReLU while converting to FP16 and write the next layer's A operand
@@ -53,8 +53,8 @@ struct __align__(16) StageDesc {
     uint16_t bytes16;  // bytes / 16
     uint16_t dcol;     // first accumulator column
     uint16_t n;        // B rows = accumulator columns covered by the stage
-    uint8_t kind;      // 0: SW128 K=64 block (4 MMAs of K=16), 1: K=16 extra block (N in chunks of 128)
-    uint8_t kb;        // activation K block (kind 0)
+    uint8_t kind;      // 0: 64B-swizzled K=32 block (2 MMAs of K=16), 1: K=16 extra block (N in chunks of 128)
+    uint8_t kb;        // index of the 32-wide K chunk of the activations (kind 0)
     uint8_t flags;     // ST_*
     uint8_t pad[3];
 };
@@ -63,6 +63,20 @@ static_assert(sizeof(StageDesc) == 16, "StageDesc layout");
 __constant__ StageDesc c_fwd[MAX_PROG];
 __constant__ StageDesc c_bwd[MAX_PROG];
 __constant__ int c_nprog[2];
+
+// What the producer and the MMA warp walk: one entry per layer of the forward ([0]) and backward ([1])
+// sweep.  The hidden stages of a layer (n in chunks of 256 outputs x k32 chunks of 32 K values, each a
+// 64B-swizzled image of min(256, n - n0) * 64 bytes) lie contiguously in the blob in consumption order.
+struct __align__(16) LayerDesc {
+    uint32_t src;    // blob offset of the first hidden stage
+    uint32_t xsrc;   // offset of the K=16 extra block (xkind 1: in the blob, 2: in the object's extras record)
+    uint16_t n;      // accumulator columns
+    uint8_t k32;     // 32-wide K chunks of the hidden part (0: extras only)
+    uint8_t xkind;   // 0: no extra block
+    uint32_t pad;
+};
+static_assert(sizeof(LayerDesc) == 16, "LayerDesc layout");
+__constant__ LayerDesc c_layers[2][8];
 
 struct TcArgs {
     DecoderDev dec;
@@ -164,64 +178,92 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     constexpr int NPROG = JAC ? 2 : 1;
 
     if (warp == 8) {
-        // ===================== weight producer (one thread) =====================
-        if (lane == 0) {
-            uint32_t s = 0, ph = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                const int obj = C::GN ? a.w.tile_obj[t] : 0;
-                const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
-                for (int p = 0; p < NPROG; ++p) {
-                    const StageDesc* prog = p ? c_bwd : c_fwd;
-                    const int np = c_nprog[p];
-                    for (int e = 0; e < np; ++e) {
-                        const StageDesc d = prog[e];
+        // ===================== weight producer (whole warp, one elected lane issues) =====================
+        uint32_t s = 0, ph = 0;
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            const int obj = C::GN ? a.w.tile_obj[t] : 0;
+            const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
+            for (int p = 0; p < NPROG; ++p) {
+#pragma unroll 1
+                for (int li = 0; li < 8; ++li) {
+                    const LayerDesc ld = c_layers[p][li];
+                    if (ld.xkind) {                              // the K=16 extra block (bias / latent / xyz)
                         mbar_wait(bar_empty(s), ph ^ 1u);
-                        const uint32_t bytes = (uint32_t)d.bytes16 * 16u;
-                        mbar_expect_tx(bar_full(s), bytes);
-                        const uint8_t* src = (d.flags & ST_OBJ) ? xo + d.src : a.blob + d.src;
-                        bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                        if (elect_one()) {
+                            const uint32_t bytes = (uint32_t)ld.n * 32u;
+                            mbar_expect_tx(bar_full(s), bytes);
+                            bulk_g2s(sST + s * STAGE_BYTES, (ld.xkind == 2 ? xo : a.blob) + ld.xsrc, bytes, bar_full(s));
+                        }
+                        __syncwarp();
                         if (++s == NST) { s = 0; ph ^= 1u; }
+                    }
+                    const uint8_t* src = a.blob + ld.src;        // hidden stages are contiguous in consumption order
+                    for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                        const uint32_t bytes = (uint32_t)min(256, (int)ld.n - n0) * 64u;
+#pragma unroll 1
+                        for (int kc = 0; kc < ld.k32; ++kc) {
+                            mbar_wait(bar_empty(s), ph ^ 1u);
+                            if (elect_one()) {
+                                mbar_expect_tx(bar_full(s), bytes);
+                                bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                            }
+                            __syncwarp();
+                            src += bytes;
+                            if (++s == NST) { s = 0; ph ^= 1u; }
+                        }
                     }
                 }
             }
         }
     } else if (warp == 9) {
-        // ===================== MMA issuer (one thread) =====================
-        if (lane == 0) {
-            uint32_t s = 0, ph = 0, aph = 0;
-            for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-                for (int p = 0; p < NPROG; ++p) {
-                    const StageDesc* prog = p ? c_bwd : c_fwd;
-                    const int np = c_nprog[p];
-                    for (int e = 0; e < np; ++e) {
-                        const StageDesc d = prog[e];
-                        if (d.flags & ST_BEGIN) {           // activations of this layer written, accumulator drained
-                            mbar_wait(bar_aready, aph);
-                            aph ^= 1u;
-                        }
+        // ===================== MMA issuer (whole warp, one elected lane issues) =====================
+        uint32_t s = 0, ph = 0, aph = 0;
+        const uint64_t adesc0 = smem_desc(sA, 16, 1024, 2);      // activations: 128B swizzle, 8-row groups 1 KB apart
+        const uint64_t bdesc0 = smem_desc(sST, 16, 512, 4);      // weight stage: 64B swizzle, 8-row groups 512 B apart
+        const uint64_t axdesc = smem_desc(sAX, 128, 256, 0);
+        const uint64_t bxdesc0 = smem_desc(sST, 128, 256, 0);
+        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+            for (int p = 0; p < NPROG; ++p) {
+#pragma unroll 1
+                for (int li = 0; li < 8; ++li) {
+                    const LayerDesc ld = c_layers[p][li];
+                    mbar_wait(bar_aready, aph);                  // this layer's A operand written, accumulator drained
+                    aph ^= 1u;
+                    if (ld.xkind) {
                         mbar_wait(bar_full(s), ph);
                         tc_fence_after();
-                        const uint32_t sB = sST + s * STAGE_BYTES;
-                        if (d.kind == 0) {
-                            const uint32_t id = idesc_f16(TILE_M, d.n);
-                            const uint32_t a0 = sA + (uint32_t)d.kb * A_BLK;
-#pragma unroll
-                            for (int ks = 0; ks < 4; ++ks)
-                                umma_f16(tmem + d.dcol, smem_desc(a0 + ks * 32, 16, 1024, 2),
-                                         smem_desc(sB + ks * 32, 16, 1024, 2), id,
-                                         ((d.flags & ST_FIRST) && ks == 0) ? 0u : 1u);
-                        } else {
-                            const uint64_t ad = smem_desc(sAX, 128, 256, 0);
-                            for (int n0 = 0; n0 < d.n; n0 += 128) {
-                                const int nn = min(128, (int)d.n - n0);
-                                umma_f16(tmem + d.dcol + n0, ad, smem_desc(sB + n0 * 32, 128, 256, 0),
-                                         idesc_f16(TILE_M, nn), (d.flags & ST_FIRST) ? 0u : 1u);
+                        if (elect_one()) {
+                            const uint64_t bx = bxdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
+                            for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                                const int nn = min(256, (int)ld.n - n0);
+                                umma_f16(tmem + n0, axdesc, bx + (uint64_t)((n0 * 32) >> 4), idesc_f16(TILE_M, nn), 0u);
                             }
+                            umma_commit(bar_empty(s));
                         }
-                        umma_commit(bar_empty(s));                       // stage reusable once these MMAs finish
-                        if (d.flags & ST_END) umma_commit(bar_dfull);    // accumulator of the layer complete
+                        __syncwarp();
                         if (++s == NST) { s = 0; ph ^= 1u; }
                     }
+                    for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                        const uint32_t id = idesc_f16(TILE_M, min(256, (int)ld.n - n0));
+                        const uint32_t dcol = tmem + n0;
+#pragma unroll 1
+                        for (int kc = 0; kc < ld.k32; ++kc) {
+                            mbar_wait(bar_full(s), ph);
+                            tc_fence_after();
+                            if (elect_one()) {
+                                // A: K chunk kc = block kc/2 (16 KB apart), half kc%2 (64 B apart); +32 B per K=16 step
+                                const uint64_t ad = adesc0 + (uint64_t)((kc >> 1) * (A_BLK >> 4) + (kc & 1) * 4);
+                                const uint64_t bd = bdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
+                                umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && kc == 0) ? 0u : 1u);
+                                umma_f16(dcol, ad + 2, bd + 2, id, 1u);
+                                umma_commit(bar_empty(s));       // stage reusable once these MMAs finish
+                            }
+                            __syncwarp();
+                            if (++s == NST) { s = 0; ph ^= 1u; }
+                        }
+                    }
+                    if (elect_one()) umma_commit(bar_dfull);     // accumulator of the layer complete
+                    __syncwarp();
                 }
             }
         }
@@ -663,14 +705,15 @@ struct BlobBuilder {
         memcpy(&h, &u, 2);
         return __half2float(h);
     }
-    // SW128 K-major image of rows [n0, n0+nn) x k in [kb*64, kb*64+64) of the matrix elem(row, k)
+    // 64-byte-swizzled K-major image of rows [n0, n0+nn) x k in [kc*32, kc*32+32) of the matrix elem(row, k):
+    // byte(r, k) = (r/8)*512 + (r%8)*64 + ((k/8) ^ ((r%8)>>1))*16 + (k%8)*2
     template <class F>
-    size_t sw128(int n0, int nn, int kb, F elem) {
-        const size_t at = alloc((size_t)nn * 128);
+    size_t sw64(int n0, int nn, int kc, F elem) {
+        const size_t at = alloc((size_t)nn * 64);
         for (int rr = 0; rr < nn; ++rr)
-            for (int k = 0; k < 64; ++k) {
-                const size_t off = (size_t)(rr >> 3) * 1024 + (size_t)(rr & 7) * 128 + (size_t)(((k >> 3) ^ (rr & 7)) << 4) + (size_t)(k & 7) * 2;
-                const uint16_t h = f2h(elem(n0 + rr, kb * 64 + k));
+            for (int k = 0; k < 32; ++k) {
+                const size_t off = (size_t)(rr >> 3) * 512 + (size_t)(rr & 7) * 64 + (size_t)(((k >> 3) ^ ((rr & 7) >> 1)) << 4) + (size_t)(k & 7) * 2;
+                const uint16_t h = f2h(elem(n0 + rr, kc * 32 + k));
                 memcpy(&bytes[at + off], &h, 2);
             }
         return at;
@@ -697,13 +740,18 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
         d.kind = (uint8_t)kind; d.kb = (uint8_t)kb; d.flags = (uint8_t)flags;
         B.prog[p].push_back(d);
     };
+    LayerDesc layers[2][8];
+    memset(layers, 0, sizeof(layers));
     // ---- forward program ----
     push(0, 0, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_END | ST_OBJ);            // layer 0: extras only
+    layers[0][0].n = HID; layers[0][0].k32 = 0; layers[0][0].xkind = 2; layers[0][0].xsrc = 0;
     for (int l = 1; l < 8; ++l) {
         const int N = (l == 3) ? h3p : HID, K = (l == 4) ? h3p : HID;
         const int Nreal = (l == 3) ? h3 : HID, Kreal = (l == 4) ? h3 : HID;
+        layers[0][l].n = (uint16_t)N; layers[0][l].k32 = (uint8_t)(K / 32);
         if (l == 4) {
             push(0, XTRA_BYTES, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_OBJ);
+            layers[0][l].xkind = 2; layers[0][l].xsrc = XTRA_BYTES;
         } else {                                                                           // static bias block
             const size_t at = B.alloc((size_t)N * 32);
             for (int n = 0; n < Nreal; ++n) {
@@ -714,16 +762,18 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
                 memcpy(&B.bytes[off + 2], &lo, 2);
             }
             push(0, at, (size_t)N * 32, 0, N, 1, 0, ST_FIRST | ST_BEGIN);
+            layers[0][l].xkind = 1; layers[0][l].xsrc = (uint32_t)at;
         }
         const float* Wl = W[l];
-        for (int n0 = 0; n0 < N; n0 += 128) {
-            const int nn = std::min(128, N - n0);
-            for (int kb = 0; kb < K / 64; ++kb) {
-                const size_t at = B.sw128(n0, nn, kb, [&](int n, int k) -> float {
+        for (int n0 = 0; n0 < N; n0 += 256) {
+            const int nn = std::min(256, N - n0);
+            for (int kb = 0; kb < K / 32; ++kb) {
+                const size_t at = B.sw64(n0, nn, kb, [&](int n, int k) -> float {
                     return (n < Nreal && k < Kreal) ? Wl[(size_t)n * HID + k] : 0.f;        // W[l] is [out][512]
                 });
-                const bool end = (n0 + nn == N) && (kb == K / 64 - 1);
-                push(0, at, (size_t)nn * 128, n0, nn, 0, kb, end ? ST_END : 0);
+                const bool end = (n0 + nn == N) && (kb == K / 32 - 1);
+                if (n0 == 0 && kb == 0) layers[0][l].src = (uint32_t)at;
+                push(0, at, (size_t)nn * 64, n0, nn, 0, kb, end ? ST_END : 0);
             }
         }
     }
@@ -731,29 +781,33 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     for (int l = 7; l >= 1; --l) {
         const int K = (l == 3) ? h3p : HID, Kreal = (l == 3) ? h3 : HID;                   // outputs of layer l
         const float* Wl = W[l];
-        for (int n0 = 0; n0 < HID; n0 += 128) {
-            for (int kb = 0; kb < K / 64; ++kb) {
-                const size_t at = B.sw128(n0, 128, kb, [&](int i, int o) -> float {
+        layers[1][7 - l].n = HID; layers[1][7 - l].k32 = (uint8_t)(K / 32);
+        for (int n0 = 0; n0 < HID; n0 += 256) {
+            for (int kb = 0; kb < K / 32; ++kb) {
+                const size_t at = B.sw64(n0, 256, kb, [&](int i, int o) -> float {
                     return (o < Kreal) ? Wl[(size_t)o * HID + i] : 0.f;
                 });
                 int fl = 0;
                 if (kb == 0) fl |= ST_FIRST;
                 if (n0 == 0 && kb == 0) fl |= ST_BEGIN;
-                if (n0 == HID - 128 && kb == K / 64 - 1) fl |= ST_END;
-                push(1, at, 128 * 128, n0, 128, 0, kb, fl);
+                if (n0 == HID - 256 && kb == K / 32 - 1) fl |= ST_END;
+                if (n0 == 0 && kb == 0) layers[1][7 - l].src = (uint32_t)at;
+                push(1, at, 256 * 64, n0, 256, 0, kb, fl);
             }
         }
     }
     {
         const int N0 = (in_dim + 15) & ~15;                                                // 80
-        for (int kb = 0; kb < HID / 64; ++kb) {
-            const size_t at = B.sw128(0, N0, kb, [&](int i, int o) -> float {
+        layers[1][7].n = (uint16_t)N0; layers[1][7].k32 = HID / 32;
+        for (int kb = 0; kb < HID / 32; ++kb) {
+            const size_t at = B.sw64(0, N0, kb, [&](int i, int o) -> float {
                 return (i < in_dim) ? W[0][(size_t)o * in_dim + i] : 0.f;
             });
             int fl = 0;
             if (kb == 0) fl |= ST_FIRST | ST_BEGIN;
-            if (kb == HID / 64 - 1) fl |= ST_END;
-            push(1, at, (size_t)N0 * 128, 0, N0, 0, kb, fl);
+            if (kb == HID / 32 - 1) fl |= ST_END;
+            if (kb == 0) layers[1][7].src = (uint32_t)at;
+            push(1, at, (size_t)N0 * 64, 0, N0, 0, kb, fl);
         }
     }
     if (B.prog[0].size() > MAX_PROG || B.prog[1].size() > MAX_PROG) { g_tc_err = "stage program too long"; return 2; }
@@ -770,6 +824,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd, B.prog[0].data(), sizeof(StageDesc) * np[0]);
     if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd, B.prog[1].data(), sizeof(StageDesc) * np[1]);
     if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_nprog, np, sizeof(np));
+    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_layers, layers, sizeof(layers));
 #define TC_ATTR(MODE)                                                                                          \
     if (e == cudaSuccess)                                                                                      \
         e = cudaFuncSetAttribute(k_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<MODE>::SMEM);
