@@ -306,3 +306,14 @@ def test_c2_sized_batch_tc_vs_fp32(eng):
         assert np.linalg.norm(Ha - Hb) / np.linalg.norm(Hb) < 3e-2
         dt, ang, _ = synth.pose_errors(a.t_cam_obj[k], b.t_cam_obj[k])
         assert dt < 1e-2 and ang < 0.1
+
+
+def test_grid_sharded_equals_single(eng):
+    """dspslam.dist.grid_sdf_sharded (world size 1 here; tools/dist_check.py runs it under torchrun + NCCL)."""
+    import torch
+    from dspslam.dist import grid_sdf_sharded
+    code = np.zeros(64, np.float32)
+    code[:3] = [0.2, -0.1, 0.3]
+    a = grid_sdf_sharded(eng, code, 24, mode="tc")
+    b = eng.grid_sdf(code, 24, mode="tc").view(24, 24, 24)
+    assert torch.equal(a, b)
