@@ -329,7 +329,7 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     return check_launch(h, nl, "dspslam_grid_sdf");
 }
 
-static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int B,
+static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int ray_phases, int B,
                   const int32_t* pts_off, const int32_t* ray_off, const int32_t* n_fg, const float* pts,
                   const float* rays, const float* depth, int64_t total_pts, int64_t total_rays, int max_pts,
                   int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
@@ -355,6 +355,12 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     if (w.jgroups_max < 1) w.jgroups_max = 1;
     w.pts_off = pts_off; w.ray_off = ray_off; w.n_fg = n_fg;
     w.pts = pts; w.rays = rays; w.depth = depth;
+    // Ray phases: 0 = choose.  Phases pay off once the batch fills the GPU several times over (every phase is
+    // at least one wave of 128-row tiles); a small batch runs one pass over all in-ball samples.  Two phases
+    // measured best on the C2 batch (B200: 1 phase 303, 2: 494, 3: 480, 4: 473 objects/s).
+    if (ray_phases < 0 || ray_phases > MAX_PHASES) return fail(DSPSLAM_E_BADARG, "ray_phases must be 0..4");
+    w.n_phases = ray_phases ? ray_phases : ((V / GROUP_ROWS >= (int64_t)h->sm_count * 8) ? 2 : 1);
+    w.phase = 0;
 
     const size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
     Carver c;
@@ -366,6 +372,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_sdf = c.take(sizeof(float) * (size_t)V);
     const size_t o_rcnt = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_roff = c.take(sizeof(int) * (size_t)total_rays);
+    const size_t o_rhit = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_jrows = c.take(sizeof(float4) * (size_t)(total_pts + V));
     const size_t o_jres = c.take(sizeof(float) * (size_t)(total_pts + V));
     const size_t o_act = c.take((size_t)total_pts);
@@ -387,6 +394,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.sdf_samp = reinterpret_cast<float*>(base + o_sdf);
     w.ray_cnt = reinterpret_cast<int*>(base + o_rcnt);
     w.ray_roff = reinterpret_cast<int*>(base + o_roff);
+    w.ray_hit = reinterpret_cast<int*>(base + o_rhit);
     w.jrows = reinterpret_cast<float4*>(base + o_jrows);
     w.jres = reinterpret_cast<float*>(base + o_jres);
     w.active = reinterpret_cast<uint8_t*>(base + o_act);
@@ -403,11 +411,15 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     for (int e = 0; e < iters; ++e) {
         launch_gn_prep(w, e, st); ++nl;
         if (!prm.pose_only) {
-            launch_gn_sample(w, st); ++nl;
-            const int pf = prof_begin(h, PK_GN_FWD, 0, st);
-            if (mode == DSPSLAM_MODE_FP32) { launch_gn_fwd_simt(w, st); ++nl; }
-            else nl += tc_launch_gn_fwd(w, h->sm_count, st);
-            prof_end(h, pf, st);
+            for (int ph = 0; ph < w.n_phases; ++ph) {      // front-to-back ray phases (k_gn_sample)
+                w.phase = ph;
+                launch_gn_sample(w, st); ++nl;
+                const int pf = prof_begin(h, PK_GN_FWD, 0, st);
+                if (mode == DSPSLAM_MODE_FP32) { launch_gn_fwd_simt(w, st); ++nl; }
+                else nl += tc_launch_gn_fwd(w, h->sm_count, st);
+                prof_end(h, pf, st);
+            }
+            w.phase = 0;
             launch_gn_ray_count(w, st); ++nl;
             launch_gn_rayscan(w, st); ++nl;
             launch_gn_ray_emit(w, st); ++nl;
@@ -438,7 +450,7 @@ int dspslam_gn_joint(dspslam_handle* h, void* stream, int mode, const dspslam_jo
     prm.pose_only = 0;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    return gn_run(h, stream, mode, prm, p->num_iterations, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
+    return gn_run(h, stream, mode, prm, p->num_iterations, p->ray_phases, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
                   total_rays, max_pts, max_rays, t_cam_obj_io, t_cam_obj_io, code_io, code_io, nullptr, status_out,
                   loss_out, dbg_out, DSPSLAM_DBG_STRIDE);
 }
@@ -461,7 +473,7 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
         CK(cudaMemset(h->zeros, 0, sizeof(int32_t) * cap));
         h->zeros_cap = cap;
     }
-    return gn_run(h, stream, mode, prm, num_iterations, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
+    return gn_run(h, stream, mode, prm, num_iterations, 1, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
                   total_pts, 0, max_pts, 0, t_co_se3_io, t_co_se3_io, code, nullptr, scale, nullptr, nullptr, dbg_out,
                   64);
 }
@@ -502,7 +514,7 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
     h->prof_rows.clear();
     out->ms_gn_fwd = ms[PK_GN_FWD]; out->ms_gn_jac = ms[PK_GN_JAC];
     out->ms_rows_fwd = ms[PK_ROWS_FWD]; out->ms_rows_jac = ms[PK_ROWS_JAC];
-    out->rows_gn_fwd = (int64_t)st[0]; out->rows_gn_jac = (int64_t)st[1];
+    out->rows_gn_fwd = (int64_t)st[0]; out->rows_gn_jac = (int64_t)st[1]; out->rows_gn_inball = (int64_t)st[2];
     out->rows_fwd = rows[PK_ROWS_FWD]; out->rows_jac = rows[PK_ROWS_JAC];
     out->n_gn_fwd = cnt[PK_GN_FWD]; out->n_gn_jac = cnt[PK_GN_JAC];
     out->n_rows_fwd = cnt[PK_ROWS_FWD]; out->n_rows_jac = cnt[PK_ROWS_JAC];

@@ -12,6 +12,8 @@ struct GnWork {
     int total_rays, total_pts;
     int jgroups_max;   // 128-row groups per object in the Jacobian kernel grid / partial slots per object
     int fgroups_max;   // 128-row groups per object in the forward (ray-sample) kernel grid
+    int n_phases;      // front-to-back ray phases per iteration (1: every in-ball sample in one pass)
+    int phase;         // phase the sample / forward launches of this view work on
     // inputs
     const int* pts_off;   // [B+1]
     const int* ray_off;   // [B+1]
@@ -29,6 +31,7 @@ struct GnWork {
     float* sdf_samp;      // [total_rays*D]  SDF per ray sample (SDF_OUTSIDE outside the ball)
     int* ray_cnt;         // [total_rays]
     int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its object
+    int* ray_hit;         // [total_rays]    first sample with sdf <= -th in the previous iteration (-1: none yet, D: no hit)
     float4* jrows;        // [total_pts + total_rays*D]  per object: M surface rows then K render rows: x,y,z,coef
     float* jres;          // same indexing: residual of render rows
     uint8_t* active;      // [total_pts]     pose-only inlier flags

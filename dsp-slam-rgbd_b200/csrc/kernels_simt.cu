@@ -122,11 +122,13 @@ __global__ void k_gn_init(GnWork w, const float* __restrict__ pose_in, const flo
         }
         inv_affine(T, s.T_oc);
         s.status = 0; s.n_valid = 0; s.K = 0; s.M_active = M;
+        for (int p = 0; p < MAX_PHASES; ++p) s.ph_rows[p] = 0;
         s.sdf_loss = 0.f; s.render_loss = 0.f; s.loss = 0.f;
     }
     for (int l = threadIdx.x; l < w.dec.L; l += blockDim.x)
         w.code[(size_t)b * MAX_L + l] = code_in[(size_t)b * code_in_stride + l];
     for (int p = threadIdx.x; p < M; p += blockDim.x) w.active[w.pts_off[b] + p] = 1;
+    for (int r = w.ray_off[b] + threadIdx.x; r < w.ray_off[b + 1]; r += blockDim.x) w.ray_hit[r] = -1;
 }
 
 // once per iteration and object: pose-derived scalars, latent biases, surface rows
@@ -148,6 +150,7 @@ __global__ void k_gn_prep(GnWork w, int iter) {
         s.dmax = s.T_co[11] + 1.0f * sc;
         s.rot_res = w.prm.pose_only ? 0.f : rot_prior(s.T_co, sc, s.rotJ);
         s.n_valid = 0;
+        for (int p = 0; p < MAX_PHASES; ++p) s.ph_rows[p] = 0;
         s.K = 0;
         cnt = 0;
     }
@@ -209,6 +212,16 @@ __global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __rest
 
 // ---------------------------------------------------------------------------
 // render term: sample generation (one warp per ray), loss.py:74-84
+//
+// The reference evaluates every in-ball sample of every ray.  The render function only needs them up
+// to the first sample with sdf <= -th: there the occupancy is exactly 1 (0.5f + th/(2 th), loss.py:98,
+// loss_utils.py:46-47), the transmittance cumprod(1-o) is exactly 0 from that sample on, so every later
+// sample contributes exactly 0 to d_u, to the acc_trans suffix sums and hence to de_do (loss.py:113-139):
+// it can never be selected and never changes a selected row.  With n_phases > 1 the samples of a ray are
+// therefore evaluated front to back in phases; a ray that has met such a sample is not continued, and the
+// samples never evaluated keep the sentinel (occupancy 0).  The result is bit-identical to n_phases = 1.
+// Phase 0 ends two samples behind the previous iteration's first hit (or at the middle of the in-ball
+// interval when there is no history), the next phases take 4, 8, ... samples and the last one the rest.
 // ---------------------------------------------------------------------------
 __global__ void k_gn_sample(GnWork w) {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -217,28 +230,67 @@ __global__ void k_gn_sample(GnWork w) {
     const int b = find_segment(w.ray_off, w.B, warp);
     ObjState& s = w.st[b];
     if (s.status != 0) return;
-    const int D = w.prm.D;
+    const int D = w.prm.D, P = w.n_phases, ph = w.phase;
     const float rx = w.rays[(size_t)warp * 3 + 0], ry = w.rays[(size_t)warp * 3 + 1],
                 rz = w.rays[(size_t)warp * 3 + 2];
     const size_t fbase = (size_t)w.ray_off[b] * D;      // this object's region of frows
-    for (int j0 = 0; j0 < D; j0 += 32) {
-        const int j = j0 + lane;
+    float xs[2], ys[2], zs[2];
+    unsigned ball[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int j = h * 32 + lane;
         bool valid = false;
-        float x = 0.f, y = 0.f, z = 0.f;
+        xs[h] = ys[h] = zs[h] = 0.f;
         if (j < D) {
             const float d = linspace_at(s.dmin, s.dmax, D, j);
-            sample_point(s.T_oc, rx, ry, rz, d, x, y, z);
-            const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z)));
+            sample_point(s.T_oc, rx, ry, rz, d, xs[h], ys[h], zs[h]);
+            const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(xs[h], xs[h]), __fmul_rn(ys[h], ys[h])),
+                                              __fmul_rn(zs[h], zs[h])));
             valid = nrm < 1.0f;                          // loss.py:82
-            if (!valid) w.sdf_samp[(size_t)warp * D + j] = SDF_OUTSIDE;
         }
-        const unsigned ball = __ballot_sync(0xffffffffu, valid);
+        ball[h] = __ballot_sync(0xffffffffu, valid);
+    }
+    const unsigned long long mask = (unsigned long long)ball[0] | ((unsigned long long)ball[1] << 32);
+    if (ph == 0 && lane == 0 && mask) atomicAdd(&s.n_valid, __popcll(mask));
+    int start = 0, end = 0, j_lo = 0;
+    if (mask) {
+        j_lo = __ffsll((long long)mask) - 1;
+        const int j_hi = 64 - __clzll((long long)mask);
+        start = j_lo; end = j_hi;
+        if (P > 1) {
+            const int pred = w.ray_hit[warp];
+            int e = (pred < 0) ? j_lo + (j_hi - j_lo + 1) / 2 : min(j_hi, pred + 3);
+            e = max(e, min(j_hi, j_lo + 1));
+            int st = j_lo;
+            for (int p = 1; p <= ph; ++p) {
+                st = e;
+                e = (p == P - 1) ? j_hi : min(j_hi, st + (4 << (p - 1)));
+            }
+            start = st; end = e;
+        }
+    }
+    if (ph > 0) {
+        if (start >= end) return;                        // (warp-uniform)
+        bool hit = false;                                // has an evaluated sample already closed the ray?
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int j = h * 32 + lane;
+            if (j >= j_lo && j < start && ((mask >> j) & 1ull)) hit |= w.sdf_samp[(size_t)warp * D + j] <= -w.prm.th;
+        }
+        if (__any_sync(0xffffffffu, hit)) return;
+    }
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+        const int j = h * 32 + lane;
+        const bool take = j < D && ((mask >> j) & 1ull) && j >= start && j < end;
+        if (ph == 0 && j < D && !take) w.sdf_samp[(size_t)warp * D + j] = SDF_OUTSIDE;
+        const unsigned tb = __ballot_sync(0xffffffffu, take);
         int base = 0;
-        if (lane == 0 && ball) base = atomicAdd(&s.n_valid, __popc(ball));
+        if (lane == 0 && tb) base = atomicAdd(&s.ph_rows[ph], __popc(tb));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (valid) {
-            const int off = __popc(ball & ((1u << lane) - 1u));
-            w.frows[fbase + base + off] = make_float4(x, y, z, __int_as_float(warp * D + j));
+        if (take) {
+            const int off = __popc(tb & ((1u << lane) - 1u));
+            w.frows[fbase + base + off] = make_float4(xs[h], ys[h], zs[h], __int_as_float(warp * D + j));
         }
     }
 }
@@ -250,7 +302,7 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_fwd_simt(GnWork w) {
     const int b = blockIdx.y, tid = threadIdx.x;
     const ObjState& s = w.st[b];
     if (s.status != 0) return;
-    const int n = s.n_valid;
+    const int n = s.ph_rows[w.phase];
     const int row0 = blockIdx.x * GROUP_ROWS;
     if (row0 >= n) return;
     const size_t fbase = (size_t)w.ray_off[b] * w.prm.D;
@@ -289,6 +341,9 @@ __global__ void k_gn_ray(GnWork w) {
     const float dobs = (local < w.n_fg[b]) ? w.depth[r] : 1.1f * s.dmax;   // optimizer.py:128
     const float* sdf = w.sdf_samp + (size_t)r * D;
     if (!EMIT) {
+        int hit = D;                                     // first closing sample: next iteration's phase-0 horizon
+        for (int j = D - 1; j >= 0; --j) if (sdf[j] <= -p.th) hit = j;
+        w.ray_hit[r] = hit;
         w.ray_cnt[r] = ray_scan(sdf, 1, dobs, p, [](int, float, float) {});
     } else {
         const int M = w.pts_off[b + 1] - w.pts_off[b];
@@ -490,7 +545,10 @@ __global__ void __launch_bounds__(256) k_gn_solve(GnWork w, int iter, float* __r
     const int M = w.pts_off[b + 1] - w.pts_off[b];
     const int K = w.prm.pose_only ? 0 : s.K;
     if (w.stats && tid == 0) {
-        atomicAdd(w.stats + 0, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
+        int evaluated = 0;
+        for (int p = 0; p < MAX_PHASES; ++p) evaluated += s.ph_rows[p];
+        atomicAdd(w.stats + 0, (unsigned long long)(w.prm.pose_only ? 0 : evaluated));
+        atomicAdd(w.stats + 2, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
         atomicAdd(w.stats + 1, (unsigned long long)(s.M_active + K));
     }
     const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;

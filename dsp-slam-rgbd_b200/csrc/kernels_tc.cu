@@ -304,7 +304,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             size_t jb = 0;
             if (MODE == 3) {
                 obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
-                rows_valid = min(TILE_M, a.w.st[obj].n_valid - row0);
+                rows_valid = min(TILE_M, a.w.st[obj].ph_rows[a.w.phase] - row0);
             } else if (MODE == 5) {
                 obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
                 M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
@@ -655,7 +655,7 @@ __global__ void k_tc_plan(GnWork w, int which) {
         const int b = base + tid;
         int nt = 0, rows = 0;
         if (b < w.B && w.st[b].status == 0) {
-            if (which == 0) rows = w.st[b].n_valid;
+            if (which == 0) rows = w.st[b].ph_rows[w.phase];
             else rows = (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : w.st[b].K);
             nt = (rows + TILE_M - 1) / TILE_M;
         }
@@ -884,12 +884,13 @@ static void pack_extras_gn(const GnWork& w, cudaStream_t st) {
 
 int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
-    pack_extras_gn(w, st);
+    int nl = 2;
+    if (w.phase == 0) { pack_extras_gn(w, st); ++nl; }   // the codes do not change between the phases of an iteration
     k_tc_plan<<<1, 1024, 0, st>>>(w, 0);
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
     launch_tc<3>(a, sm_count, st);
-    return 3;
+    return nl;
 }
 
 int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {

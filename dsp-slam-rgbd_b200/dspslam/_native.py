@@ -33,13 +33,13 @@ class JointParams(C.Structure):
     _fields_ = [("k1", C.c_float), ("k2", C.c_float), ("k3", C.c_float), ("k4", C.c_float),
                 ("b1", C.c_float), ("b2", C.c_float), ("lr", C.c_float), ("s_damp", C.c_float),
                 ("cut_off", C.c_float), ("num_iterations", C.c_int32),
-                ("num_depth_samples", C.c_int32), ("reserved", C.c_int32)]
+                ("num_depth_samples", C.c_int32), ("ray_phases", C.c_int32)]
 
 
 class Profile(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("ms_gn_fwd", "ms_gn_jac", "ms_rows_fwd", "ms_rows_jac")] + \
                [(n, C.c_int64) for n in ("rows_gn_fwd", "rows_gn_jac", "rows_fwd", "rows_jac",
-                                         "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac")]
+                                         "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac", "rows_gn_inball")]
 
 
 class NativeError(RuntimeError):

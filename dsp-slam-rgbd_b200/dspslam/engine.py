@@ -223,7 +223,7 @@ class Engine:
         io[o["codes"]: o["codes"] + 4 * L * B].copy_(io[o["codes0"]: o["codes0"] + 4 * L * B])
         prm = N.JointParams(params["k1"], params["k2"], params["k3"], params["k4"], params["b1"], params["b2"],
                             params["lr"], params["s_damp"], params["cut_off"], params["num_iterations"],
-                            params["num_depth_samples"], 0)
+                            params["num_depth_samples"], int(params.get("ray_phases", 0)))
         dbg = None
         if debug:
             dbg = t.zeros((max(1, params["num_iterations"]), B, N.DBG_STRIDE), dtype=t.float32, device=self.device)

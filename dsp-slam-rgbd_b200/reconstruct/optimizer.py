@@ -40,8 +40,11 @@ def _engine_for(decoder, device=None, mode="tc"):
 
 
 class Optimizer(object):
-    def __init__(self, decoder, configs, mode="tc", device=None, verbose=False):
+    def __init__(self, decoder, configs, mode="tc", device=None, verbose=False, ray_phases=0):
         self.decoder = decoder
+        # render term: 1 = evaluate every in-ball ray sample (as the reference does), 2..4 = stop rays at their
+        # first fully occupied sample (bit-identical, fewer decoder queries), 0 = let the library choose
+        self.ray_phases = ray_phases
         optim_cfg = configs.optimizer
         self.k1 = optim_cfg.joint_optim.k1
         self.k2 = optim_cfg.joint_optim.k2
@@ -66,7 +69,7 @@ class Optimizer(object):
     def _params(self):
         return dict(k1=self.k1, k2=self.k2, k3=self.k3, k4=self.k4, b1=self.b1, b2=self.b2, lr=self.lr,
                     s_damp=self.s_damp, cut_off=self.cut_off, num_iterations=self.num_iterations_joint_optim,
-                    num_depth_samples=self.num_depth_samples)
+                    num_depth_samples=self.num_depth_samples, ray_phases=self.ray_phases)
 
     # ---- pose only (stereo+LiDAR re-observation), optimizer.py:46-87 ------------------------
     def estimate_pose_cam_obj(self, t_co_se3, scale, pts, code):

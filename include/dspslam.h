@@ -107,7 +107,10 @@ typedef struct {
     float cut_off;        /* cut_off_threshold (occupancy band)               */
     int32_t num_iterations;
     int32_t num_depth_samples; /* <= 64 */
-    int32_t reserved;
+    int32_t ray_phases;        /* render term: front-to-back passes over the ray samples per iteration.
+                                * 1 evaluates every in-ball sample like the reference; 2..4 stop a ray at its first
+                                * sample with sdf <= -cut_off (occupancy exactly 1, transmittance exactly 0 behind
+                                * it: bit-identical results, fewer decoder queries); 0 lets the library choose. */
 } dspslam_joint_params;
 
 /* A batch of B independent detections, concatenated.
@@ -142,13 +145,14 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
  * `get_time()` prints.  Off by default; enabling it costs two event records per decoder launch.
  *   ms_*     summed event time of the forward-only decoder launches of the GN loop (ray samples), the
  *            SDF+Jacobian launches of the GN loop, and the stand-alone sdf / sdf_jac / grid launches
- *   rows_*   rows those launches were asked to evaluate (GN: in-ball samples; active surface + render rows)
+ *   rows_*   rows those launches were asked to evaluate (GN: ray samples evaluated; active surface + render rows)
  *   n_*      number of launches in each class
  * dspslam_profile_read synchronises the recorded events, returns the totals since the last read and resets. */
 typedef struct {
     double ms_gn_fwd, ms_gn_jac, ms_rows_fwd, ms_rows_jac;
     int64_t rows_gn_fwd, rows_gn_jac, rows_fwd, rows_jac;
     int64_t n_gn_fwd, n_gn_jac, n_rows_fwd, n_rows_jac;
+    int64_t rows_gn_inball; /* in-ball ray samples of the GN loop (what the reference evaluates; >= rows_gn_fwd) */
 } dspslam_profile;
 int dspslam_profile_enable(dspslam_handle* h, int on);
 int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out);

@@ -317,3 +317,31 @@ def test_grid_sharded_equals_single(eng):
     a = grid_sdf_sharded(eng, code, 24, mode="tc")
     b = eng.grid_sdf(code, 24, mode="tc").view(24, 24, 24)
     assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_ray_phases_bit_identical(mode, eng):
+    """Early ray termination (dspslam_joint_params.ray_phases): a ray is not sampled behind its first sample with
+    sdf <= -th, where occupancy is exactly 1 and the transmittance exactly 0 (loss.py:98-139).  Every phase count
+    must give bit-identical H, b, poses and codes, while the decoder evaluates fewer rows."""
+    from dspslam import synth
+    dets = [synth.make_kitti_detection(k, M=300 + 40 * k, n_bg=80 + 9 * k) for k in range(4)]
+    base, rows = None, {}
+    for ph in (1, 2, 3, 4):
+        p = dict(params(synth.kitti_config(), iters=4), ray_phases=ph)
+        eng.profile_enable(True)
+        r = eng.gn_joint(dets, p, mode=mode, debug=True)
+        prof = eng.profile_read()
+        eng.profile_enable(False)
+        rows[ph] = (prof["rows_gn_fwd"], prof["rows_gn_inball"])
+        assert (r.status == 0).all()
+        if base is None:
+            base = r
+            assert prof["rows_gn_fwd"] == prof["rows_gn_inball"] > 0      # one pass evaluates every in-ball sample
+            continue
+        assert np.array_equal(r.status, base.status)
+        assert np.array_equal(r.dbg, base.dbg)
+        assert np.array_equal(r.t_cam_obj, base.t_cam_obj) and np.array_equal(r.code, base.code)
+        assert np.array_equal(r.loss, base.loss)
+        assert prof["rows_gn_inball"] == rows[1][1]
+        assert prof["rows_gn_fwd"] < 0.8 * rows[1][0]
