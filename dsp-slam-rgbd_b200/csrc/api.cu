@@ -373,13 +373,19 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_rcnt = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_roff = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_rhit = c.take(sizeof(int) * (size_t)total_rays);
+    const size_t o_rres = c.take(sizeof(float) * (size_t)total_rays);
+    const size_t o_dtab = c.take(sizeof(float) * 64 * (size_t)B);
+    const size_t o_dobj = c.take(sizeof(unsigned int) * (size_t)B);
+    const int ray_chunks = max_rays > 0 ? (max_rays + 127) / 128 : 1;
+    const size_t o_cc = c.take(sizeof(int) * (size_t)B * ray_chunks);
     const size_t o_jrows = c.take(sizeof(float4) * (size_t)(total_pts + V));
     const size_t o_jres = c.take(sizeof(float) * (size_t)(total_pts + V));
     const size_t o_act = c.take((size_t)total_pts);
     const size_t o_sres = c.take(sizeof(float) * (size_t)total_pts);
     const size_t o_tobj = c.take(sizeof(int) * max_tiles);
     const size_t o_trow = c.take(sizeof(int) * max_tiles);
-    const size_t o_ntl = c.take(sizeof(int) * 8);
+    const size_t o_ntl = c.take(sizeof(int) * 8);            // n_tiles[2] | done[2]
+    const size_t o_toff = c.take(sizeof(int) * ((size_t)B + 1));
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
     const size_t o_xtra = c.take(mode == DSPSLAM_MODE_TC ? tc_xtra_bytes_per_object() * (size_t)B : 0);
     if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
@@ -395,6 +401,11 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.ray_cnt = reinterpret_cast<int*>(base + o_rcnt);
     w.ray_roff = reinterpret_cast<int*>(base + o_roff);
     w.ray_hit = reinterpret_cast<int*>(base + o_rhit);
+    w.ray_res = reinterpret_cast<float*>(base + o_rres);
+    w.dtab = reinterpret_cast<float*>(base + o_dtab);
+    w.done_obj = reinterpret_cast<unsigned int*>(base + o_dobj);
+    w.chunk_cnt = reinterpret_cast<int*>(base + o_cc);
+    w.ray_chunks = ray_chunks;
     w.jrows = reinterpret_cast<float4*>(base + o_jrows);
     w.jres = reinterpret_cast<float*>(base + o_jres);
     w.active = reinterpret_cast<uint8_t*>(base + o_act);
@@ -402,14 +413,22 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.tile_obj = reinterpret_cast<int*>(base + o_tobj);
     w.tile_row0 = reinterpret_cast<int*>(base + o_trow);
     w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
+    w.done = reinterpret_cast<unsigned int*>(base + o_ntl) + 4;
+    w.tile_off = reinterpret_cast<int*>(base + o_toff);
+    w.tc = (mode == DSPSLAM_MODE_TC) ? 1 : 0;
     w.partials = reinterpret_cast<float*>(base + o_part);
     w.stats = h->prof_on ? h->stats : nullptr;
     w.tc_xtra = reinterpret_cast<uint8_t*>(base + o_xtra);
 
+    // Launch sequence per iteration (no host synchronisation anywhere): [sample -> forward decoder] x phases ->
+    // rays -> SDF+Jacobian decoder -> solve.  The tile lists of the decoder kernels are planned by the last CTA of
+    // the kernel in front of them; solve also prepares the next iteration (pose scalars, latent biases, rows).
     int nl = 0;
+    CK(cudaMemsetAsync(base + o_ntl, 0, sizeof(int) * 8, st));
+    CK(cudaMemsetAsync(base + o_dobj, 0, sizeof(unsigned int) * (size_t)B, st));
     launch_gn_init(w, pose_in, code_in, h->dec.L, scale_in, st); ++nl;
+    if (iters > 0) { launch_gn_prep(w, 0, st); ++nl; }
     for (int e = 0; e < iters; ++e) {
-        launch_gn_prep(w, e, st); ++nl;
         if (!prm.pose_only) {
             for (int ph = 0; ph < w.n_phases; ++ph) {      // front-to-back ray phases (k_gn_sample)
                 w.phase = ph;
@@ -420,15 +439,13 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                 prof_end(h, pf, st);
             }
             w.phase = 0;
-            launch_gn_ray_count(w, st); ++nl;
-            launch_gn_rayscan(w, st); ++nl;
-            launch_gn_ray_emit(w, st); ++nl;
+            launch_gn_rays(w, max_rays, st); nl += 2;
         }
         const int pj = prof_begin(h, PK_GN_JAC, 0, st);
         if (mode == DSPSLAM_MODE_FP32) { launch_gn_jac_simt(w, st); ++nl; }
         else nl += tc_launch_gn_jac(w, h->sm_count, st);
         prof_end(h, pj, st);
-        launch_gn_solve(w, e, dbg_out, dbg_stride, st); ++nl;
+        launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); ++nl;
     }
     launch_gn_final(w, pose_out, code_out, h->dec.L, scale_in, status_out, loss_out, st); ++nl;
     return check_launch(h, nl, "dspslam_gn");

@@ -186,9 +186,14 @@ struct RayParams {
     float th;          // cut-off threshold
     float dmin, dmax;  // depth range (sampled_depth[0], sampled_depth[D-1])
     int D;
+    const float* dtab; // null, or the D sampled depths (linspace_at(dmin, dmax, D, j)) precomputed per object
 };
 
 #define DSP_MAX_D 64
+
+DSP_HD float ray_depth(const RayParams& p, int j) {
+    return p.dtab ? p.dtab[j] : linspace_at(p.dmin, p.dmax, p.D, j);
+}
 
 template <class Emit>
 DSP_HD int ray_scan(const float* sdf, int stride, float depth_obs, const RayParams& p, Emit emit) {
@@ -196,27 +201,30 @@ DSP_HD int ray_scan(const float* sdf, int stride, float depth_obs, const RayPara
     float acc[DSP_MAX_D];
     // pass 1: transmittance acc_j = prod_{i<=j} (1-o_i) and expected depth
     //         d_u = sum_j d_j * o_j * acc_{j-1} + 1.1*dmax * acc_{D-1}
+    // Once the transmittance is exactly 0 every later term is exactly 0: stop there (jend).
     float T = 1.f, d_u = 0.f;
+    int jend = D;
     for (int j = 0; j < D; ++j) {
         float s = sdf[j * stride];
         float o = 0.5f - fminf(fmaxf(s, -p.th), p.th) / (2.f * p.th);
-        d_u += linspace_at(p.dmin, p.dmax, D, j) * (o * T);
+        d_u += ray_depth(p, j) * (o * T);
         T *= (1.f - o);
         acc[j] = T;
+        if (T == 0.f) { jend = j + 1; break; }
     }
     d_u += (1.1f * p.dmax) * T;
     float res = depth_obs - d_u;
     res = fminf(fmaxf(res, -0.30f), 0.30f);
     // pass 2 (backwards): acc[k] <- sum_{j>=k} acc_j
     float suffix = 0.f;
-    for (int k = D - 1; k >= 0; --k) {
+    for (int k = jend - 1; k >= 0; --k) {
         suffix += acc[k];
         acc[k] = suffix;
     }
     const float delta_d = (p.dmax - p.dmin) / (float)(D - 1);
     const float do_ds = -1.f / (2.f * p.th);
     int n = 0;
-    for (int k = 0; k < D; ++k) {
+    for (int k = 0; k < jend; ++k) {
         float s = sdf[k * stride];
         if (s > -p.th && s < p.th) {
             float o = 0.5f - s / (2.f * p.th);

@@ -14,7 +14,7 @@ float hd_linspace_at(float a, float b, int n, int i) { return dsp::linspace_at(a
 int hd_ray_scan(const float* sdf, int D, float depth_obs, float th, float dmin, float dmax, int* idx,
                 float* de_ds, float* res) {
     dsp::RayParams p;
-    p.th = th; p.dmin = dmin; p.dmax = dmax; p.D = D;
+    p.th = th; p.dmin = dmin; p.dmax = dmax; p.D = D; p.dtab = nullptr;
     int n = 0;
     return dsp::ray_scan(sdf, 1, depth_obs, p, [&](int k, float a, float r) {
         idx[n] = k; de_ds[n] = a; res[n] = r; ++n;

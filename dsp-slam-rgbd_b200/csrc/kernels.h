@@ -27,10 +27,14 @@ struct GnWork {
     float* c0;            // [B][512] latent bias of layer 0
     float* c4;            // [B][512] latent bias of layer 4
     // scratch
-    float4* frows;        // [total_rays*D]  compacted in-ball samples per object: x,y,z,dest
+    float4* frows;        // [total_rays*D]  compacted in-ball samples per object: x,y,z,dest; after the forward
+                          //                 phases: staging of the selected render rows, ray r at [r*D, r*D+cnt)
     float* sdf_samp;      // [total_rays*D]  SDF per ray sample (SDF_OUTSIDE outside the ball)
     int* ray_cnt;         // [total_rays]
-    int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its object
+    int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its 128-ray chunk
+    int* chunk_cnt;       // [B][ray_chunks] rows selected by each chunk of rays, then (scanned) the chunk's first row
+    int ray_chunks;       // 128-ray chunks per object in the k_gn_ray_count grid (from max_rays)
+    float* ray_res;       // [total_rays]    depth residual of the ray (shared by all its selected rows)
     int* ray_hit;         // [total_rays]    first sample with sdf <= -th in the previous iteration (-1: none yet, D: no hit)
     float4* jrows;        // [total_pts + total_rays*D]  per object: M surface rows then K render rows: x,y,z,coef
     float* jres;          // same indexing: residual of render rows
@@ -41,6 +45,11 @@ struct GnWork {
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object
     int* n_tiles;         // [2] number of forward / Jacobian tiles
+    int* tile_off;        // [B+1] first tile of each object in the list being planned (scratch of plan_tiles)
+    unsigned int* done;   // [2] "last CTA done" tickets of k_gn_sample / k_gn_ray_count (zero between launches)
+    unsigned int* done_obj; // [B] per-object tickets of k_gn_ray_count
+    float* dtab;          // [B][64] sampled ray depths of the iteration (linspace(dmin, dmax, D), optimizer.py:126)
+    int tc;               // 1: tcgen05 mode (extras images and tile lists are maintained)
     uint8_t* tc_xtra;     // [B][2][16 KB] per-object extra blocks of layers 0 and 4 (kernels_tc.cu)
     unsigned long long* stats;  // null or [2]: algorithmic rows evaluated (forward-only, SDF+Jacobian)
 };
@@ -63,10 +72,8 @@ void launch_gn_final(const GnWork& w, float* pose_out, float* code_out, int code
                      int* status_out, float* loss_out, cudaStream_t st);
 void launch_gn_sample(const GnWork& w, cudaStream_t st);
 void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st);
-void launch_gn_ray_count(const GnWork& w, cudaStream_t st);
-void launch_gn_ray_emit(const GnWork& w, cudaStream_t st);
-void launch_gn_rayscan(const GnWork& w, cudaStream_t st);
+void launch_gn_rays(const GnWork& w, int max_rays, cudaStream_t st);
 void launch_gn_jac_simt(const GnWork& w, cudaStream_t st);
-void launch_gn_solve(const GnWork& w, int iter, float* dbg, int dbg_stride, cudaStream_t st);
+void launch_gn_solve(const GnWork& w, int iter, int last_iter, float* dbg, int dbg_stride, cudaStream_t st);
 
 }  // namespace dsp

@@ -2,6 +2,7 @@
 // libdspslam_sm100.  See common.cuh / mlp_simt.cuh / hd_math.h for the pieces and
 // include/dspslam.h for the reference lines each entry point replaces.
 #include "kernels.h"
+#include "gn_device.cuh"
 #include "mlp_simt.cuh"
 
 namespace dsp {
@@ -131,13 +132,14 @@ __global__ void k_gn_init(GnWork w, const float* __restrict__ pose_in, const flo
     for (int r = w.ray_off[b] + threadIdx.x; r < w.ray_off[b + 1]; r += blockDim.x) w.ray_hit[r] = -1;
 }
 
-// once per iteration and object: pose-derived scalars, latent biases, surface rows
-__global__ void k_gn_prep(GnWork w, int iter) {
+// once per iteration and object: pose-derived scalars, latent biases (and, in tcgen05 mode, the extra-block
+// images built from them), surface rows in the object frame.  Called by every thread of the object's CTA
+// (k_gn_prep before the first iteration, k_gn_solve after each update); status must be 0.
+__device__ void prep_object(const GnWork& w, int b, int iter) {
     __shared__ float z[MAX_L];
     __shared__ int cnt;
-    const int b = blockIdx.x, tid = threadIdx.x;
+    const int tid = threadIdx.x;
     ObjState& s = w.st[b];
-    if (s.status != 0) return;
     const int p0 = w.pts_off[b], M = w.pts_off[b + 1] - p0;
     if (tid == 0) {
         inv_affine(s.T_oc, s.T_co);
@@ -156,14 +158,22 @@ __global__ void k_gn_prep(GnWork w, int iter) {
     }
     if (tid < w.dec.L) z[tid] = w.code[(size_t)b * MAX_L + tid];
     __syncthreads();
+    if (tid < w.prm.D) w.dtab[(size_t)b * 64 + tid] = linspace_at(s.dmin, s.dmax, w.prm.D, tid);
     for (int n = tid; n < HID; n += blockDim.x) {
         float s0 = 0.f, s4 = 0.f;
         for (int l = 0; l < w.dec.L; ++l) {
             s0 = fmaf(__ldg(w.dec.Wt0 + (size_t)l * HID + n), z[l], s0);
             s4 = fmaf(__ldg(w.dec.W4in + (size_t)l * HID + n), z[l], s4);
         }
-        w.c0[(size_t)b * HID + n] = s0 + __ldg(w.dec.bias[0] + n);
-        w.c4[(size_t)b * HID + n] = s4 + __ldg(w.dec.bias[4] + n);
+        s0 += __ldg(w.dec.bias[0] + n);
+        s4 += __ldg(w.dec.bias[4] + n);
+        w.c0[(size_t)b * HID + n] = s0;
+        w.c4[(size_t)b * HID + n] = s4;
+        if (w.tc) {
+            uint8_t* img = w.tc_xtra + (size_t)b * (2 * XTRA_BYTES);
+            pack_extra_row(w.dec, 0, n, s0, img);
+            pack_extra_row(w.dec, 1, n, s4, img + XTRA_BYTES);
+        }
     }
     // pose-only inlier cut after iteration e == 4 (optimizer.py:77-79)
     const bool cut = w.prm.pose_only && iter == 5;
@@ -186,6 +196,13 @@ __global__ void k_gn_prep(GnWork w, int iter) {
         __syncthreads();
         if (tid == 0) s.M_active = cnt;
     }
+}
+
+__global__ void k_gn_prep(GnWork w, int iter) {
+    const int b = blockIdx.x;
+    if (w.st[b].status == 0) prep_object(w, b, iter);       // (CTA-uniform)
+    // pose-only runs have no ray kernels: the Jacobian tile list of the first iteration is planned here
+    if (w.tc && w.prm.pose_only && last_cta_done(w.done + 1)) plan_tiles(w, 1);
 }
 
 __global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __restrict__ code_out,
@@ -223,76 +240,111 @@ __global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __rest
 // Phase 0 ends two samples behind the previous iteration's first hit (or at the middle of the in-ball
 // interval when there is no history), the next phases take 4, 8, ... samples and the last one the rest.
 // ---------------------------------------------------------------------------
-__global__ void k_gn_sample(GnWork w) {
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (warp >= w.total_rays) return;
-    const int b = find_segment(w.ray_off, w.B, warp);
-    ObjState& s = w.st[b];
-    if (s.status != 0) return;
+__global__ void __launch_bounds__(256) k_gn_sample(GnWork w) {
+    __shared__ int s_obj, s_cnt, s_nv, s_base;
+    const int tid = threadIdx.x;
+    const int warp = (blockIdx.x * blockDim.x + tid) >> 5;
+    const int lane = tid & 31;
     const int D = w.prm.D, P = w.n_phases, ph = w.phase;
-    const float rx = w.rays[(size_t)warp * 3 + 0], ry = w.rays[(size_t)warp * 3 + 1],
-                rz = w.rays[(size_t)warp * 3 + 2];
-    const size_t fbase = (size_t)w.ray_off[b] * D;      // this object's region of frows
-    float xs[2], ys[2], zs[2];
-    unsigned ball[2];
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int j = h * 32 + lane;
-        bool valid = false;
-        xs[h] = ys[h] = zs[h] = 0.f;
-        if (j < D) {
-            const float d = linspace_at(s.dmin, s.dmax, D, j);
-            sample_point(s.T_oc, rx, ry, rz, d, xs[h], ys[h], zs[h]);
-            const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(xs[h], xs[h]), __fmul_rn(ys[h], ys[h])),
-                                              __fmul_rn(zs[h], zs[h])));
-            valid = nrm < 1.0f;                          // loss.py:82
-        }
-        ball[h] = __ballot_sync(0xffffffffu, valid);
+    int b = -1;
+    bool live = false;
+    if (warp < w.total_rays) {
+        b = find_segment(w.ray_off, w.B, warp);
+        live = w.st[b].status == 0;
     }
-    const unsigned long long mask = (unsigned long long)ball[0] | ((unsigned long long)ball[1] << 32);
-    if (ph == 0 && lane == 0 && mask) atomicAdd(&s.n_valid, __popcll(mask));
-    int start = 0, end = 0, j_lo = 0;
-    if (mask) {
-        j_lo = __ffsll((long long)mask) - 1;
-        const int j_hi = 64 - __clzll((long long)mask);
-        start = j_lo; end = j_hi;
-        if (P > 1) {
-            const int pred = w.ray_hit[warp];
-            int e = (pred < 0) ? j_lo + (j_hi - j_lo + 1) / 2 : min(j_hi, pred + 3);
-            e = max(e, min(j_hi, j_lo + 1));
-            int st = j_lo;
-            for (int p = 1; p <= ph; ++p) {
-                st = e;
-                e = (p == P - 1) ? j_hi : min(j_hi, st + (4 << (p - 1)));
-            }
-            start = st; end = e;
-        }
-    }
-    if (ph > 0) {
-        if (start >= end) return;                        // (warp-uniform)
-        bool hit = false;                                // has an evaluated sample already closed the ray?
+    if (tid == 0) { s_obj = b; s_cnt = 0; s_nv = 0; }
+    float xs[2] = {0.f, 0.f}, ys[2] = {0.f, 0.f}, zs[2] = {0.f, 0.f};
+    unsigned tb[2] = {0u, 0u};
+    unsigned long long mask = 0ull;
+    if (live) {                                            // (warp-uniform)
+        const ObjState& s = w.st[b];
+        const float rx = w.rays[(size_t)warp * 3 + 0], ry = w.rays[(size_t)warp * 3 + 1],
+                    rz = w.rays[(size_t)warp * 3 + 2];
+        unsigned ball[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             const int j = h * 32 + lane;
-            if (j >= j_lo && j < start && ((mask >> j) & 1ull)) hit |= w.sdf_samp[(size_t)warp * D + j] <= -w.prm.th;
+            bool valid = false;
+            if (j < D) {
+                const float d = w.dtab[(size_t)b * 64 + j];
+                sample_point(s.T_oc, rx, ry, rz, d, xs[h], ys[h], zs[h]);
+                const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(xs[h], xs[h]), __fmul_rn(ys[h], ys[h])),
+                                                  __fmul_rn(zs[h], zs[h])));
+                valid = nrm < 1.0f;                      // loss.py:82
+            }
+            ball[h] = __ballot_sync(0xffffffffu, valid);
         }
-        if (__any_sync(0xffffffffu, hit)) return;
-    }
+        mask = (unsigned long long)ball[0] | ((unsigned long long)ball[1] << 32);
+        int start = 0, end = 0, j_lo = 0;
+        if (mask) {
+            j_lo = __ffsll((long long)mask) - 1;
+            const int j_hi = 64 - __clzll((long long)mask);
+            start = j_lo; end = j_hi;
+            if (P > 1) {
+                const int pred = w.ray_hit[warp];
+                int e = (pred < 0) ? j_lo + (j_hi - j_lo + 1) / 2 : min(j_hi, pred + 3);
+                e = max(e, min(j_hi, j_lo + 1));
+                int st = j_lo;
+                for (int p = 1; p <= ph; ++p) {
+                    st = e;
+                    e = (p == P - 1) ? j_hi : min(j_hi, st + (4 << (p - 1)));
+                }
+                start = st; end = e;
+            }
+        }
+        if (ph > 0 && start < end) {                     // has an evaluated sample already closed the ray?
+            bool hit = false;
 #pragma unroll
-    for (int h = 0; h < 2; ++h) {
-        const int j = h * 32 + lane;
-        const bool take = j < D && ((mask >> j) & 1ull) && j >= start && j < end;
-        if (ph == 0 && j < D && !take) w.sdf_samp[(size_t)warp * D + j] = SDF_OUTSIDE;
-        const unsigned tb = __ballot_sync(0xffffffffu, take);
-        int base = 0;
-        if (lane == 0 && tb) base = atomicAdd(&s.ph_rows[ph], __popc(tb));
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (take) {
-            const int off = __popc(tb & ((1u << lane) - 1u));
-            w.frows[fbase + base + off] = make_float4(xs[h], ys[h], zs[h], __int_as_float(warp * D + j));
+            for (int h = 0; h < 2; ++h) {
+                const int j = h * 32 + lane;
+                if (j >= j_lo && j < start && ((mask >> j) & 1ull))
+                    hit |= w.sdf_samp[(size_t)warp * D + j] <= -w.prm.th;
+            }
+            if (__any_sync(0xffffffffu, hit)) end = start;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int j = h * 32 + lane;
+            const bool take = j < D && ((mask >> j) & 1ull) && j >= start && j < end;
+            if (ph == 0 && j < D && !take) w.sdf_samp[(size_t)warp * D + j] = SDF_OUTSIDE;
+            tb[h] = __ballot_sync(0xffffffffu, take);
         }
     }
+    // row slots: one shared-memory atomic per ray, one global atomic per CTA (rays of the CTA's first object)
+    __syncthreads();
+    const int cnt = __popc(tb[0]) + __popc(tb[1]);
+    const int nv = (ph == 0) ? __popcll(mask) : 0;
+    const bool mine = live && b == s_obj;
+    int base = 0;
+    if (lane == 0 && live) {
+        if (mine) {
+            if (cnt) base = atomicAdd(&s_cnt, cnt);
+            if (nv) atomicAdd(&s_nv, nv);
+        } else {
+            if (cnt) base = atomicAdd(&w.st[b].ph_rows[ph], cnt);
+            if (nv) atomicAdd(&w.st[b].n_valid, nv);
+        }
+    }
+    __syncthreads();
+    if (tid == 0 && s_obj >= 0) {
+        if (s_cnt) s_base = atomicAdd(&w.st[s_obj].ph_rows[ph], s_cnt);
+        if (s_nv) atomicAdd(&w.st[s_obj].n_valid, s_nv);
+    }
+    __syncthreads();
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (mine) base += s_base;
+    if (cnt) {
+        const size_t fbase = (size_t)w.ray_off[b] * D;  // this object's region of frows
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int j = h * 32 + lane;
+            if ((tb[h] >> lane) & 1u) {
+                const int off = __popc(tb[h] & ((1u << lane) - 1u)) + (h ? __popc(tb[0]) : 0);
+                w.frows[fbase + base + off] = make_float4(xs[h], ys[h], zs[h], __int_as_float(warp * D + j));
+            }
+        }
+    }
+    if (w.tc && last_cta_done(w.done + 0)) plan_tiles(w, 0);
 }
 
 // forward-only SDF of the compacted in-ball samples, FP32 path (grid: groups x objects)
@@ -325,83 +377,127 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_fwd_simt(GnWork w) {
 }
 
 // ---------------------------------------------------------------------------
-// render term: per-ray scan (thread per ray), count then emit.  loss.py:98-155
+// render term: per-ray scan, loss.py:98-155.
+//   k_gn_ray_count  grid (ray chunks, objects), thread per ray.  The chunk's SDF samples are staged through shared
+//                   memory (coalesced loads, conflict-free pitch).  Each thread runs the scan once and stages the
+//                   rows it selects at frows[ray*D + m] (the forward phases are done with that buffer), the
+//                   ray's residual in ray_res, and the row offset of the ray inside its chunk.  The last CTA of an
+//                   object scans the chunk totals (rows end up in ray order: deterministic J^T J summation order),
+//                   sets K and the status; the last CTA of the grid plans the Jacobian tile list of the tcgen05
+//                   kernel.
+//   k_gn_ray_emit   thread per ray: copies the staged rows behind the object's surface rows.
 // ---------------------------------------------------------------------------
-template <bool EMIT>
-__global__ void k_gn_ray(GnWork w) {
-    const int r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= w.total_rays) return;
-    const int b = find_segment(w.ray_off, w.B, r);
-    const ObjState& s = w.st[b];
-    if (s.status != 0) { if (!EMIT) w.ray_cnt[r] = 0; return; }
-    const int D = w.prm.D;
-    RayParams p;
-    p.th = w.prm.th; p.dmin = s.dmin; p.dmax = s.dmax; p.D = D;
-    const int local = r - w.ray_off[b];
-    const float dobs = (local < w.n_fg[b]) ? w.depth[r] : 1.1f * s.dmax;   // optimizer.py:128
-    const float* sdf = w.sdf_samp + (size_t)r * D;
-    if (!EMIT) {
-        int hit = D;                                     // first closing sample: next iteration's phase-0 horizon
-        for (int j = D - 1; j >= 0; --j) if (sdf[j] <= -p.th) hit = j;
-        w.ray_hit[r] = hit;
-        w.ray_cnt[r] = ray_scan(sdf, 1, dobs, p, [](int, float, float) {});
-    } else {
-        const int M = w.pts_off[b + 1] - w.pts_off[b];
-        size_t at = (size_t)w.pts_off[b] + (size_t)w.ray_off[b] * D + M + w.ray_roff[r];
-        const float rx = w.rays[(size_t)r * 3 + 0], ry = w.rays[(size_t)r * 3 + 1], rz = w.rays[(size_t)r * 3 + 2];
-        ray_scan(sdf, 1, dobs, p, [&](int k, float de_ds, float res) {
-            float x, y, z;
-            sample_point(s.T_oc, rx, ry, rz, linspace_at(s.dmin, s.dmax, D, k), x, y, z);
-            w.jrows[at] = make_float4(x, y, z, de_ds);
-            w.jres[at] = res;
-            ++at;
-        });
-    }
-}
-template __global__ void k_gn_ray<false>(GnWork);
-template __global__ void k_gn_ray<true>(GnWork);
+constexpr int RAY_NT = 128;
 
-// exclusive scan of the per-ray row counts of one object (CTA per object) + status
-__global__ void k_gn_rayscan(GnWork w) {
-    __shared__ int warp_sums[32];
-    __shared__ int carry;
-    const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+__global__ void __launch_bounds__(RAY_NT) k_gn_ray_count(GnWork w) {
+    extern __shared__ float s_sdf[];                           // [RAY_NT][D + 1]
+    __shared__ int s_part[RAY_NT];
+    __shared__ int s_last_obj;
+    const int b = blockIdx.y, tid = threadIdx.x;
     ObjState& s = w.st[b];
-    if (s.status != 0) return;
+    const int D = w.prm.D, pitch = D + 1;
     const int r0 = w.ray_off[b], N = w.ray_off[b + 1] - r0;
-    if (tid == 0) carry = 0;
-    __syncthreads();
-    for (int base = 0; base < N; base += blockDim.x) {
-        const int i = base + tid;
-        const int v = (i < N) ? w.ray_cnt[r0 + i] : 0;
-        int inc = v;
+    const int i0 = blockIdx.x * RAY_NT;
+    const bool live = s.status == 0;                           // (CTA-uniform)
+    int my_cnt = 0;
+    if (live && i0 < N) {
+        const int nr = min(RAY_NT, N - i0);
+        const float* src = w.sdf_samp + (size_t)(r0 + i0) * D;
+        for (int e = tid; e < nr * D; e += RAY_NT) s_sdf[(e / D) * pitch + (e % D)] = src[e];
+        __syncthreads();
+        if (tid < nr) {
+            const int i = i0 + tid, r = r0 + i;
+            RayParams p;
+            p.th = w.prm.th; p.dmin = s.dmin; p.dmax = s.dmax; p.D = D; p.dtab = w.dtab + (size_t)b * 64;
+            const float* sdf = s_sdf + tid * pitch;
+            const float dobs = (i < w.n_fg[b]) ? w.depth[r] : 1.1f * s.dmax;   // optimizer.py:128
+            int hit = D;                                 // first closing sample: next iteration's phase-0 horizon
+            for (int j = D - 1; j >= 0; --j) if (sdf[j] <= -p.th) hit = j;
+            w.ray_hit[r] = hit;
+            const float rx = w.rays[(size_t)r * 3 + 0], ry = w.rays[(size_t)r * 3 + 1], rz = w.rays[(size_t)r * 3 + 2];
+            float4* stage = w.frows + (size_t)r * D;
+            float res_ray = 0.f;
+            const int cnt = ray_scan(sdf, 1, dobs, p, [&](int k, float de_ds, float res) {
+                float x, y, z;
+                sample_point(s.T_oc, rx, ry, rz, p.dtab[k], x, y, z);
+                *stage++ = make_float4(x, y, z, de_ds);
+                res_ray = res;
+            });
+            my_cnt = cnt;
+            w.ray_cnt[r] = cnt;
+            w.ray_res[r] = res_ray;
+        }
+    }
+    // ---- row offsets inside the chunk (ray order) and the chunk total ----
+    {
+        const int lane = tid & 31, wid = tid >> 5;
+        int inc = my_cnt;
         for (int o = 1; o < 32; o <<= 1) {
             const int t = __shfl_up_sync(0xffffffffu, inc, o);
             if (lane >= o) inc += t;
         }
-        if (lane == 31) warp_sums[wid] = inc;
+        if (lane == 31) s_part[wid] = inc;
         __syncthreads();
-        if (wid == 0) {
-            int ws = (lane < (int)(blockDim.x >> 5)) ? warp_sums[lane] : 0;
-            int winc = ws;
-            for (int o = 1; o < 32; o <<= 1) {
-                const int t = __shfl_up_sync(0xffffffffu, winc, o);
-                if (lane >= o) winc += t;
-            }
-            warp_sums[lane] = winc - ws;                // exclusive warp offsets
-            if (lane == 31) warp_sums[31] = winc;       // (blockDim <= 992: slot 31 free) total of this chunk
+        int wbase = 0, total = 0;
+#pragma unroll
+        for (int q = 0; q < RAY_NT / 32; ++q) {
+            const int v = s_part[q];
+            if (q < wid) wbase += v;
+            total += v;
         }
-        __syncthreads();
-        const int chunk_total = warp_sums[31];
-        if (i < N) w.ray_roff[r0 + i] = carry + warp_sums[wid] + inc - v;
-        __syncthreads();
-        if (tid == 0) carry += chunk_total;
-        __syncthreads();
+        if (live && i0 + tid < N) w.ray_roff[r0 + i0 + tid] = wbase + inc - my_cnt;
+        if (tid == 0) w.chunk_cnt[(size_t)b * w.ray_chunks + blockIdx.x] = live ? total : 0;
     }
+    // ---- last CTA of the object: exclusive scan of its chunk totals ----
+    __threadfence();
+    __syncthreads();
     if (tid == 0) {
-        s.K = carry;
-        if (s.n_valid < 10) s.status = 1;               // loss.py:87-88
-        else if (carry == 0) s.status = 2;              // mean over 0 rows = NaN (optimizer.py:150-152)
+        const unsigned ticket = atomicAdd(w.done_obj + b, 1u);
+        s_last_obj = (ticket == gridDim.x - 1);
+        if (s_last_obj) w.done_obj[b] = 0;
+    }
+    __syncthreads();
+    if (s_last_obj && live && tid < 32) {
+        __threadfence();
+        int* cc = w.chunk_cnt + (size_t)b * w.ray_chunks;
+        int carry = 0;
+        for (int base = 0; base < w.ray_chunks; base += 32) {
+            const int x = base + tid;
+            const int v = (x < w.ray_chunks) ? __ldcg(cc + x) : 0;
+            int inc = v;
+            for (int o = 1; o < 32; o <<= 1) {
+                const int t = __shfl_up_sync(0xffffffffu, inc, o);
+                if (tid >= o) inc += t;
+            }
+            if (x < w.ray_chunks) cc[x] = carry + inc - v;     // in place: count -> first row of the chunk
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (tid == 0) {
+            s.K = carry;
+            if (*(volatile int*)&s.n_valid < 10) s.status = 1;   // loss.py:87-88
+            else if (carry == 0) s.status = 2;          // mean over 0 rows = NaN (optimizer.py:150-152)
+        }
+    }
+    if (w.tc && last_cta_done(w.done + 1)) plan_tiles(w, 1);
+}
+
+__global__ void k_gn_ray_emit(GnWork w) {
+    const int r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= w.total_rays) return;
+    const int cnt = w.ray_cnt[r];
+    if (cnt == 0) return;                                       // (also rays of failed objects: counts stay 0)
+    const int b = find_segment(w.ray_off, w.B, r);
+    if (w.st[b].status != 0) return;
+    const int D = w.prm.D;
+    const int M = w.pts_off[b + 1] - w.pts_off[b];
+    const int chunk = (r - w.ray_off[b]) / RAY_NT;
+    size_t at = (size_t)w.pts_off[b] + (size_t)w.ray_off[b] * D + M + w.chunk_cnt[(size_t)b * w.ray_chunks + chunk] +
+                w.ray_roff[r];
+    const float4* stage = w.frows + (size_t)r * D;
+    const float res = w.ray_res[r];
+    for (int m = 0; m < cnt; ++m, ++at) {
+        w.jrows[at] = stage[m];
+        w.jres[at] = res;
     }
 }
 
@@ -523,10 +619,20 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_jac_simt(GnWork w) {
 }
 
 // ---------------------------------------------------------------------------
-// normal equations: reduce partials, priors + damping, Cholesky solve, update.
-// optimizer.py:157-194 (joint) / :69-75 (pose only).  One CTA per object.
+// normal equations: reduce partials, priors + damping, solve, update, and the preparation of the next
+// iteration.  optimizer.py:157-194 (joint) / :69-75 (pose only).  One CTA per object.
+//
+// The reference solves with torch.inverse(H) b in FP32.  Here H (symmetric positive definite after damping)
+// is factorised in FP64 as L D L^T, left-looking, one barrier per column: thread i owns row i; column j is
+//   w_ij = H_ij - sum_{k<j} u_ik w_jk,   D_j = w_jj,   u_ij = w_ij / D_j  (= L_ij)
+// with w kept in the lower triangle and u in the (otherwise redundant) upper triangle, transposed, so that a
+// thread's own-row reads are conflict-free and the pivot row is a broadcast.  b rides along as row `dim`
+// (its u lives in xs), which makes the forward substitution part of the same loop.
 // ---------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_gn_solve(GnWork w, int iter, float* __restrict__ dbg, int dbg_stride) {
+constexpr int SOLVE_NT = 512;
+
+__global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int last_iter, float* __restrict__ dbg,
+                                                       int dbg_stride) {
     __shared__ double Hs[(HMAX + 1) * HMAX];
     __shared__ double xs[HMAX + 1];
     __shared__ float losses[2];
@@ -535,125 +641,161 @@ __global__ void __launch_bounds__(256) k_gn_solve(GnWork w, int iter, float* __r
     ObjState& s = w.st[b];
     float* dbg_o = dbg ? dbg + ((size_t)iter * w.B + b) * dbg_stride : nullptr;
     const int L = w.dec.L, n = POSE + L;
-    if (s.status != 0) {
-        if (dbg_o && tid == 0 && !w.prm.pose_only) {
-            dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
-            dbg_o[PART_LOSS + 5] = (float)s.status;
+    bool live = s.status == 0;                                 // (CTA-uniform)
+    if (!live && dbg_o && tid == 0 && !w.prm.pose_only) {
+        dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
+        dbg_o[PART_LOSS + 5] = (float)s.status;
+    }
+    if (live) {
+        const int M = w.pts_off[b + 1] - w.pts_off[b];
+        const int K = w.prm.pose_only ? 0 : s.K;
+        if (w.stats && tid == 0) {
+            int evaluated = 0;
+            for (int p = 0; p < MAX_PHASES; ++p) evaluated += s.ph_rows[p];
+            atomicAdd(w.stats + 0, (unsigned long long)(w.prm.pose_only ? 0 : evaluated));
+            atomicAdd(w.stats + 1, (unsigned long long)(s.M_active + K));
+            atomicAdd(w.stats + 2, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
         }
-        return;
-    }
-    const int M = w.pts_off[b + 1] - w.pts_off[b];
-    const int K = w.prm.pose_only ? 0 : s.K;
-    if (w.stats && tid == 0) {
-        int evaluated = 0;
-        for (int p = 0; p < MAX_PHASES; ++p) evaluated += s.ph_rows[p];
-        atomicAdd(w.stats + 0, (unsigned long long)(w.prm.pose_only ? 0 : evaluated));
-        atomicAdd(w.stats + 2, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
-        atomicAdd(w.stats + 1, (unsigned long long)(s.M_active + K));
-    }
-    const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;
-    const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
-    for (int e = tid; e < n * n + n; e += blockDim.x) {
-        double a = 0.0;
-        for (int g = 0; g < ng; ++g) a += (double)part[(size_t)g * PART_STRIDE + e];
-        Hs[e] = a;                      // rows 0..n-1: H, row n: b
-    }
-    if (tid < 2) {
-        float a = 0.f;
-        for (int g = 0; g < ng; ++g) a += part[(size_t)g * PART_STRIDE + PART_LOSS + tid];
-        losses[tid] = a / (tid == 0 ? (float)s.M_active : (float)K);     // mean of robust_res^2
-    }
-    __syncthreads();
-    if (tid == 0) {
-        const float sl = losses[0], rl = w.prm.pose_only ? 0.f : losses[1];
-        fail = (sl != sl) || (rl != rl);                 // math.isnan checks (optimizer.py:137,151)
-        if (!fail) { s.sdf_loss = sl; s.render_loss = rl; }
-    }
-    __syncthreads();
-    if (fail) {
-        if (tid == 0) { s.status = 2; if (dbg_o && !w.prm.pose_only) dbg_o[PART_LOSS + 5] = 2.f; }
-        return;
-    }
-    int dim;
-    if (!w.prm.pose_only) {
-        dim = n;
-        if (tid < L) {                                                  // code prior (optimizer.py:172-174)
-            Hs[(POSE + tid) * n + POSE + tid] += (double)w.prm.k3;
-            Hs[n * n + POSE + tid] -= (double)w.prm.k3 * (double)w.code[(size_t)b * MAX_L + tid];
-        }
-        if (tid == 64) {                                                // rotation prior (:177-181)
-            for (int i = 0; i < 3; ++i) {
-                for (int j = 0; j < 3; ++j)
-                    Hs[(3 + i) * n + 3 + j] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rotJ[j];
-                Hs[n * n + 3 + i] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rot_res;
+        const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;
+        const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
+        for (int e = tid; e < n * n + n; e += SOLVE_NT) {
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int g = 0;
+            for (; g + 4 <= ng; g += 4) {                       // fixed summation order: ((g0+g4+..)+(g1+..))+...
+                a0 += (double)part[(size_t)(g + 0) * PART_STRIDE + e];
+                a1 += (double)part[(size_t)(g + 1) * PART_STRIDE + e];
+                a2 += (double)part[(size_t)(g + 2) * PART_STRIDE + e];
+                a3 += (double)part[(size_t)(g + 3) * PART_STRIDE + e];
             }
+            for (; g < ng; ++g) a0 += (double)part[(size_t)g * PART_STRIDE + e];
+            Hs[e] = (a0 + a1) + (a2 + a3);                      // rows 0..n-1: H, row n: b
+        }
+        if (tid < 2) {
+            float a = 0.f;
+            for (int g = 0; g < ng; ++g) a += part[(size_t)g * PART_STRIDE + PART_LOSS + tid];
+            losses[tid] = a / (tid == 0 ? (float)s.M_active : (float)K);     // mean of robust_res^2
         }
         __syncthreads();
-        if (tid < POSE) Hs[tid * n + tid] += 1.0 + (tid == POSE - 1 ? (double)w.prm.s_damp : 0.0);   // :185-186
-    } else {
-        dim = 6;
-        // move b (row n) next to the 6x6 block as row 6 so that the factorisation below sees [H; b^T]
-        if (tid < 6) xs[tid] = Hs[n * n + tid];
+        if (tid == 0) {
+            const float sl = losses[0], rl = w.prm.pose_only ? 0.f : losses[1];
+            fail = (sl != sl) || (rl != rl);                 // math.isnan checks (optimizer.py:137,151)
+            if (!fail) { s.sdf_loss = sl; s.render_loss = rl; }
+            else { s.status = 2; if (dbg_o && !w.prm.pose_only) dbg_o[PART_LOSS + 5] = 2.f; }
+        }
         __syncthreads();
-        if (tid < 6) { Hs[6 * n + tid] = xs[tid]; Hs[tid * n + tid] += 1e-2; }          // :71
+        live = !fail;
     }
-    __syncthreads();
-    if (dbg_o) {
+    if (live) {
+        int dim;
         if (!w.prm.pose_only) {
-            for (int e = tid; e < n * n + n; e += blockDim.x) dbg_o[e] = (float)Hs[e];
-            if (tid == 0) {
-                dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
-                dbg_o[PART_LOSS + 2] = s.sdf_loss; dbg_o[PART_LOSS + 3] = s.render_loss;
-                dbg_o[PART_LOSS + 4] = s.scale;    dbg_o[PART_LOSS + 5] = 0.f;
+            dim = n;
+            if (tid < L) {                                                  // code prior (optimizer.py:172-174)
+                Hs[(POSE + tid) * n + POSE + tid] += (double)w.prm.k3;
+                Hs[n * n + POSE + tid] -= (double)w.prm.k3 * (double)w.code[(size_t)b * MAX_L + tid];
             }
-        } else if (tid < 42) {
-            dbg_o[tid] = (float)Hs[(tid / 6) * n + (tid % 6)];          // 6x6 H then b
-            if (tid == 0) dbg_o[42] = (float)s.M_active;
-        }
-        __syncthreads();
-    }
-    // Cholesky of H with b^T carried as row `dim`:  afterwards row dim holds y = L^-1 b
-    for (int j = 0; j < dim; ++j) {
-        if (tid == 0) Hs[j * n + j] = sqrt(Hs[j * n + j]);
-        __syncthreads();
-        const double d = Hs[j * n + j];
-        for (int i = j + 1 + tid; i <= dim; i += blockDim.x) Hs[i * n + j] /= d;
-        __syncthreads();
-        const int cnt = dim - j;                        // rows j+1 .. dim
-        for (int e = tid; e < cnt * cnt; e += blockDim.x) {
-            const int i = j + 1 + e / cnt, k = j + 1 + e % cnt;
-            if (k <= i && k < dim) Hs[i * n + k] -= Hs[i * n + j] * Hs[k * n + j];
-        }
-        __syncthreads();
-    }
-    // back substitution L^T x = y  (warp 0)
-    if (tid < 32) {
-        for (int j = dim - 1; j >= 0; --j) {
-            double a = 0.0;
-            for (int i = j + 1 + tid; i < dim; i += 32) a += Hs[i * n + j] * xs[i];
-            for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-            if (tid == 0) xs[j] = (Hs[dim * n + j] - a) / Hs[j * n + j];
-            __syncwarp();
-        }
-    }
-    __syncthreads();
-    // update (optimizer.py:189-194 / :73-75)
-    if (tid == 0) {
-        float dp[7], dT[16], Tn[16];
-        if (!w.prm.pose_only) {
-            for (int i = 0; i < 7; ++i) dp[i] = w.prm.lr * (float)xs[i];
-            exp_sim3(dp, dT);
+            if (tid == 64) {                                                // rotation prior (:177-181)
+                for (int i = 0; i < 3; ++i) {
+                    for (int j = 0; j < 3; ++j)
+                        Hs[(3 + i) * n + 3 + j] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rotJ[j];
+                    Hs[n * n + 3 + i] += (double)w.prm.k4 * (double)s.rotJ[i] * (double)s.rot_res;
+                }
+            }
+            __syncthreads();
+            if (tid < POSE) Hs[tid * n + tid] += 1.0 + (tid == POSE - 1 ? (double)w.prm.s_damp : 0.0);   // :185-186
         } else {
-            for (int i = 0; i < 6; ++i) dp[i] = (float)xs[i];
-            exp_se3(dp, dT);
+            dim = 6;
+            // move b (row n) next to the 6x6 block as row 6 so that the factorisation below sees [H; b^T]
+            if (tid < 6) xs[tid] = Hs[n * n + tid];
+            __syncthreads();
+            if (tid < 6) { Hs[6 * n + tid] = xs[tid]; Hs[tid * n + tid] += 1e-2; }          // :71
         }
-        mul_affine(dT, s.T_oc, Tn);
-        for (int i = 0; i < 16; ++i) s.T_oc[i] = Tn[i];
-        if (!w.prm.pose_only) s.loss = w.prm.k1 * s.render_loss + w.prm.k2 * s.sdf_loss;
-        else s.loss = s.sdf_loss;
+        __syncthreads();
+        if (dbg_o) {
+            if (!w.prm.pose_only) {
+                for (int e = tid; e < n * n + n; e += SOLVE_NT) dbg_o[e] = (float)Hs[e];
+                if (tid == 0) {
+                    dbg_o[PART_LOSS + 0] = (float)s.K; dbg_o[PART_LOSS + 1] = (float)s.n_valid;
+                    dbg_o[PART_LOSS + 2] = s.sdf_loss; dbg_o[PART_LOSS + 3] = s.render_loss;
+                    dbg_o[PART_LOSS + 4] = s.scale;    dbg_o[PART_LOSS + 5] = 0.f;
+                }
+            } else if (tid < 42) {
+                dbg_o[tid] = (float)Hs[(tid / 6) * n + (tid % 6)];          // 6x6 H then b
+                if (tid == 0) dbg_o[42] = (float)s.M_active;
+            }
+            __syncthreads();
+        }
+        // L D L^T, left-looking; thread i = row i (row dim = b)
+        {
+            const int i = tid;
+            for (int j = 0; j < dim; ++j) {
+                double acc = 0.0;
+                if (i >= j && i <= dim) {
+                    double a0 = Hs[i * n + j], a1 = 0.0;
+                    const double* wj = Hs + j * n;
+                    if (i < dim) {
+                        int k = 0;
+                        for (; k + 2 <= j; k += 2) {
+                            a0 = fma(-Hs[k * n + i], wj[k], a0);
+                            a1 = fma(-Hs[(k + 1) * n + i], wj[k + 1], a1);
+                        }
+                        if (k < j) a0 = fma(-Hs[k * n + i], wj[k], a0);
+                    } else {
+                        int k = 0;
+                        for (; k + 2 <= j; k += 2) {
+                            a0 = fma(-xs[k], wj[k], a0);
+                            a1 = fma(-xs[k + 1], wj[k + 1], a1);
+                        }
+                        if (k < j) a0 = fma(-xs[k], wj[k], a0);
+                    }
+                    acc = a0 + a1;
+                    Hs[i * n + j] = acc;
+                }
+                __syncthreads();
+                if (i > j && i <= dim) {
+                    const double u = acc / Hs[j * n + j];
+                    if (i < dim) Hs[j * n + i] = u; else xs[j] = u;
+                }
+            }
+        }
+        __syncthreads();
+        // back substitution L^T x = y (y = xs), column-oriented, warp 0: lane holds x[lane], x[lane+32], x[lane+64]
+        if (tid < 32) {
+            double x0 = (tid < dim) ? xs[tid] : 0.0, x1 = (tid + 32 < dim) ? xs[tid + 32] : 0.0,
+                   x2 = (tid + 64 < dim) ? xs[tid + 64] : 0.0;
+            for (int c = dim - 1; c > 0; --c) {
+                const double own = (c < 32) ? x0 : (c < 64 ? x1 : x2);
+                const double xc = __shfl_sync(0xffffffffu, own, c & 31);
+                const double* uc = Hs + c;                                   // u_cj = L_cj at Hs[j*n + c]
+                if (tid < c) x0 = fma(-uc[tid * n], xc, x0);
+                if (tid + 32 < c) x1 = fma(-uc[(tid + 32) * n], xc, x1);
+                if (tid + 64 < c) x2 = fma(-uc[(tid + 64) * n], xc, x2);
+            }
+            if (tid < dim) xs[tid] = x0;
+            if (tid + 32 < dim) xs[tid + 32] = x1;
+            if (tid + 64 < dim) xs[tid + 64] = x2;
+        }
+        __syncthreads();
+        // update (optimizer.py:189-194 / :73-75)
+        if (tid == 0) {
+            float dp[7], dT[16], Tn[16];
+            if (!w.prm.pose_only) {
+                for (int i = 0; i < 7; ++i) dp[i] = w.prm.lr * (float)xs[i];
+                exp_sim3(dp, dT);
+            } else {
+                for (int i = 0; i < 6; ++i) dp[i] = (float)xs[i];
+                exp_se3(dp, dT);
+            }
+            mul_affine(dT, s.T_oc, Tn);
+            for (int i = 0; i < 16; ++i) s.T_oc[i] = Tn[i];
+            if (!w.prm.pose_only) s.loss = w.prm.k1 * s.render_loss + w.prm.k2 * s.sdf_loss;
+            else s.loss = s.sdf_loss;
+        }
+        if (!w.prm.pose_only && tid < L)
+            w.code[(size_t)b * MAX_L + tid] += w.prm.lr * (float)xs[POSE + tid];
+        __syncthreads();
+        if (!last_iter) prep_object(w, b, iter + 1);            // next iteration's pose scalars, latent biases, rows
     }
-    if (!w.prm.pose_only && tid < L)
-        w.code[(size_t)b * MAX_L + tid] += w.prm.lr * (float)xs[POSE + tid];
+    if (w.tc && w.prm.pose_only && !last_iter && last_cta_done(w.done + 1)) plan_tiles(w, 1);
 }
 
 // ---------------------------------------------------------------------------
@@ -708,28 +850,23 @@ void launch_gn_final(const GnWork& w, float* pose_out, float* code_out, int code
     k_gn_final<<<w.B, 64, 0, st>>>(w, pose_out, code_out, code_stride, scale_in, status_out, loss_out);
 }
 void launch_gn_sample(const GnWork& w, cudaStream_t st) {
-    if (w.total_rays == 0) return;
-    const int64_t threads = (int64_t)w.total_rays * 32;
-    k_gn_sample<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(w);
+    const int64_t threads = (int64_t)w.total_rays * 32;       // (no rays: one CTA that only plans an empty tile list)
+    k_gn_sample<<<(unsigned)((threads + 255) / 256 > 0 ? (threads + 255) / 256 : 1), 256, 0, st>>>(w);
 }
 void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st) {
     if (w.fgroups_max == 0) return;
     k_gn_fwd_simt<<<dim3(w.fgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);
 }
-void launch_gn_ray_count(const GnWork& w, cudaStream_t st) {
-    if (w.total_rays == 0) return;
-    k_gn_ray<false><<<(w.total_rays + 127) / 128, 128, 0, st>>>(w);
+void launch_gn_rays(const GnWork& w, int max_rays, cudaStream_t st) {
+    const int chunks = w.ray_chunks;
+    k_gn_ray_count<<<dim3(chunks, w.B), RAY_NT, sizeof(float) * RAY_NT * (w.prm.D + 1), st>>>(w);
+    k_gn_ray_emit<<<(w.total_rays + 255) / 256 > 0 ? (w.total_rays + 255) / 256 : 1, 256, 0, st>>>(w);
 }
-void launch_gn_ray_emit(const GnWork& w, cudaStream_t st) {
-    if (w.total_rays == 0) return;
-    k_gn_ray<true><<<(w.total_rays + 127) / 128, 128, 0, st>>>(w);
-}
-void launch_gn_rayscan(const GnWork& w, cudaStream_t st) { k_gn_rayscan<<<w.B, 256, 0, st>>>(w); }
 void launch_gn_jac_simt(const GnWork& w, cudaStream_t st) {
     k_gn_jac_simt<<<dim3(w.jgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);
 }
-void launch_gn_solve(const GnWork& w, int iter, float* dbg, int dbg_stride, cudaStream_t st) {
-    k_gn_solve<<<w.B, 256, 0, st>>>(w, iter, dbg, dbg_stride);
+void launch_gn_solve(const GnWork& w, int iter, int last_iter, float* dbg, int dbg_stride, cudaStream_t st) {
+    k_gn_solve<<<w.B, SOLVE_NT, 0, st>>>(w, iter, last_iter, dbg, dbg_stride);
 }
 
 }  // namespace dsp

@@ -25,6 +25,7 @@
 #include <string>
 #include <vector>
 
+#include "gn_device.cuh"
 #include "tc_ptx.cuh"
 
 namespace dsp {
@@ -39,8 +40,7 @@ constexpr int A_BLK = 16384;       // one K=64 block of the activation tile: 128
 constexpr int A_BYTES = 8 * A_BLK;
 constexpr int AX_BYTES = 4096;     // the K=16 extra block of the tile: 128 rows x 32 B, no swizzle
 constexpr int STAGE_BYTES = 16384;
-constexpr int XTRA_BYTES = 16384;  // one extra-block B image: 512 rows x 32 B
-constexpr int JLD = 73;            // row stride (floats) of the per-row Jacobian buffer
+constexpr int JLD = 76;            // row stride (floats) of the per-row Jacobian buffer (float4-aligned rows)
 constexpr float GSCALE = 256.f;    // gradients are carried scaled so that FP16 keeps them normal
 constexpr int MAX_PROG = 256;
 constexpr int TMEM_COLS = 512;
@@ -114,11 +114,6 @@ struct Cfg {
 
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
     asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-
-__device__ __forceinline__ void split_f16(float v, __half& hi, __half& lo) {
-    hi = __float2half_rn(v);
-    lo = __float2half_rn(v - __half2float(hi));
 }
 
 __device__ __forceinline__ void build_pose_row(float* J, float gx, float gy, float gz, float x, float y, float z) {
@@ -525,6 +520,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                             if (i < L) jr[POSE + i] = cf * (dval(i) + jr[i]) * inv_s;
                         }
                         build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
+                        for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;    // padding columns of the 4x4 blocks
                     }
                 }
                 tc_fence_before();
@@ -565,29 +561,53 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         rts[r] = rt;
                     }
                     named_bar_sync(1, EPI_THREADS);
+                    // H is symmetric: 4x4 register blocks (bi <= bj) over the 128 rows, mirrored on the way out;
+                    // the threads left over take J^T r.  ~23 instructions per row and block instead of 3 shared
+                    // loads per multiply-add (the element-per-thread version was 27 % of the kernel).
                     const int n = POSE + L;
-                    constexpr int NQ = (HMAX * HMAX + HMAX + EPI_THREADS - 1) / EPI_THREADS;   // 20
-                    float acc[NQ];
-#pragma unroll
-                    for (int qn = 0; qn < NQ; ++qn) {
-                        const int e = etid + qn * EPI_THREADS;
-                        float s = 0.f;
-                        if (e < n * n) {
-                            const int i = e / n, j = e - i * n;
-                            for (int row = 0; row < TILE_M; ++row)
-                                s = fmaf(wrows[row] * jrow[row * JLD + i], jrow[row * JLD + j], s);
-                        } else if (e < n * n + n) {
-                            const int i = e - n * n;
-                            for (int row = 0; row < TILE_M; ++row)
-                                s = fmaf(-wrows[row] * jrow[row * JLD + i], rts[row], s);
-                        }
-                        acc[qn] = s;
-                    }
+                    const int nb = (n + 3) >> 2;
+                    const int nblk = nb * (nb + 1) / 2;
                     float* part = w.partials + ((size_t)obj * w.jgroups_max + (row0 / GROUP_ROWS)) * PART_STRIDE;
+                    if (etid < nblk) {
+                        int bi = 0, rem = etid;                  // block (bi, bj), bi <= bj, row-major over the upper triangle
+                        while (rem >= nb - bi) { rem -= nb - bi; ++bi; }
+                        const int bj = bi + rem;
+                        float acc[4][4];
 #pragma unroll
-                    for (int qn = 0; qn < NQ; ++qn) {
-                        const int e = etid + qn * EPI_THREADS;
-                        if (e < n * n + n) part[e] = acc[qn];
+                        for (int p = 0; p < 4; ++p)
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) acc[p][q] = 0.f;
+                        const float* ja = jrow + 4 * bi;
+                        const float* jb4 = jrow + 4 * bj;
+#pragma unroll 4
+                        for (int row = 0; row < TILE_M; ++row) {
+                            const float wr = wrows[row];
+                            const float4 av = *reinterpret_cast<const float4*>(ja + row * JLD);
+                            const float4 bv = *reinterpret_cast<const float4*>(jb4 + row * JLD);
+                            const float a4[4] = {wr * av.x, wr * av.y, wr * av.z, wr * av.w};
+                            const float b4[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                                for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(a4[p], b4[q], acc[p][q]);
+                        }
+#pragma unroll
+                        for (int p = 0; p < 4; ++p)
+#pragma unroll
+                            for (int q = 0; q < 4; ++q) {
+                                const int i = 4 * bi + p, j = 4 * bj + q;
+                                if (i < n && j < n) {
+                                    part[i * n + j] = acc[p][q];
+                                    if (bi != bj) part[j * n + i] = acc[p][q];
+                                }
+                            }
+                    } else {
+                        for (int i = etid - nblk; i < n; i += EPI_THREADS - nblk) {
+                            float sacc = 0.f;
+                            for (int row = 0; row < TILE_M; ++row)
+                                sacc = fmaf(-wrows[row] * jrow[row * JLD + i], rts[row], sacc);
+                            part[n * n + i] = sacc;
+                        }
                     }
                     if (hc == 0) {                                           // loss sums over the 128 rows
                         for (int o = 16; o > 0; o >>= 1) {
@@ -618,62 +638,13 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// per-object extra blocks of layers 0 and 4 (B operand of the K=16 MMA):
-//   k=0,1: hi/lo of the latent bias c (k_latent_bias / k_gn_prep);  k=2..4: hi(W_xyz) (x x_hi);
-//   k=5..7: hi(W_xyz) (x x_lo);  k=8..10: lo(W_xyz) (x x_hi)
-// image layout (no swizzle, K-major): byte(n, k) = (n/8)*256 + (k/8)*128 + (n%8)*16 + (k%8)*2
+// extra blocks of layers 0 and 4 for the single-code entry points (gn_device.cuh: pack_extra_row; the GN
+// drivers build theirs inside k_gn_prep / k_gn_solve)
 // ------------------------------------------------------------------------------------------------
 __global__ void k_tc_pack_extra(DecoderDev dec, const float* __restrict__ c0, const float* __restrict__ c4,
-                                const int* __restrict__ status, int stride_st, uint8_t* __restrict__ xtra) {
-    const int b = blockIdx.x, which = blockIdx.y, n = threadIdx.x;
-    if (status && *reinterpret_cast<const int*>(reinterpret_cast<const char*>(status) + (size_t)b * stride_st) != 0) return;
-    const float bias = which ? c4[(size_t)b * HID + n] : c0[(size_t)b * HID + n];
-    float wx[3];
-    for (int c = 0; c < 3; ++c)
-        wx[c] = which ? __ldg(dec.W4in + (size_t)(dec.L + c) * HID + n) : __ldg(dec.W0x4 + (size_t)c * HID + n);
-    __half h[16];
-    for (int k = 0; k < 16; ++k) h[k] = __float2half_rn(0.f);
-    split_f16(bias, h[0], h[1]);
-    for (int c = 0; c < 3; ++c) {
-        __half hi, lo;
-        split_f16(wx[c], hi, lo);
-        h[2 + c] = hi; h[5 + c] = hi; h[8 + c] = lo;
-    }
-    uint8_t* dst = xtra + ((size_t)b * 2 + which) * XTRA_BYTES + (size_t)(n >> 3) * 256 + (size_t)(n & 7) * 16;
-    *reinterpret_cast<uint4*>(dst) = *reinterpret_cast<const uint4*>(&h[0]);
-    *reinterpret_cast<uint4*>(dst + 128) = *reinterpret_cast<const uint4*>(&h[8]);
-}
-
-// work lists of the GN kernels: 128-row tiles per object (objects that failed get none)
-__global__ void k_tc_plan(GnWork w, int which) {
-    __shared__ int s_scan[1024];
-    __shared__ int s_carry;
-    const int tid = threadIdx.x;
-    if (tid == 0) s_carry = 0;
-    __syncthreads();
-    for (int base = 0; base < w.B; base += blockDim.x) {
-        const int b = base + tid;
-        int nt = 0, rows = 0;
-        if (b < w.B && w.st[b].status == 0) {
-            if (which == 0) rows = w.st[b].ph_rows[w.phase];
-            else rows = (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : w.st[b].K);
-            nt = (rows + TILE_M - 1) / TILE_M;
-        }
-        s_scan[tid] = nt;
-        __syncthreads();
-        for (int o = 1; o < (int)blockDim.x; o <<= 1) {           // Hillis-Steele inclusive scan
-            int v = (tid >= o) ? s_scan[tid - o] : 0;
-            __syncthreads();
-            s_scan[tid] += v;
-            __syncthreads();
-        }
-        const int first = s_carry + s_scan[tid] - nt;
-        for (int i = 0; i < nt; ++i) { w.tile_obj[first + i] = b; w.tile_row0[first + i] = i * TILE_M; }
-        __syncthreads();
-        if (tid == (int)blockDim.x - 1) s_carry += s_scan[tid];
-        __syncthreads();
-    }
-    if (tid == 0) w.n_tiles[which] = s_carry;
+                                uint8_t* __restrict__ xtra) {
+    const int which = blockIdx.y, n = threadIdx.x;
+    pack_extra_row(dec, which, n, which ? c4[n] : c0[n], xtra + (size_t)which * XTRA_BYTES);
 }
 
 }  // namespace tc
@@ -724,7 +695,7 @@ struct BlobBuilder {
 
 const char* tc_last_error() { return g_tc_err.c_str(); }
 
-size_t tc_xtra_bytes_per_object() { return 2 * (size_t)tc::XTRA_BYTES; }
+size_t tc_xtra_bytes_per_object() { return 2 * (size_t)XTRA_BYTES; }
 
 int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* const* b, __half** hblob) {
     using namespace tc;
@@ -851,7 +822,7 @@ void launch_tc(const tc::TcArgs& a, int grid, cudaStream_t st) {
 int tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, int64_t i0, int G,
                        int src_mode, const float* c0, const float* c4, float* out, cudaStream_t st) {
     using namespace tc;
-    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, nullptr, 0, dec.tc_xtra1);
+    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, dec.tc_xtra1);
     TcArgs a{};
     a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
     a.xyz = xyz; a.n = n; a.i0 = i0; a.G = G; a.out = out;
@@ -866,7 +837,7 @@ int tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, in
 int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
                       const float* c4, float* sdf_out, float* jac_out, cudaStream_t st) {
     using namespace tc;
-    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, nullptr, 0, dec.tc_xtra1);
+    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, dec.tc_xtra1);
     TcArgs a{};
     a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
     a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
@@ -875,33 +846,22 @@ int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int
     return 2;
 }
 
-// per-object extras are packed once per iteration (by the forward launch, or by the Jacobian launch in
-// the ray-less pose-only driver)
-static void pack_extras_gn(const GnWork& w, cudaStream_t st) {
-    tc::k_tc_pack_extra<<<dim3(w.B, 2), HID, 0, st>>>(w.dec, w.c0, w.c4, &w.st[0].status, (int)sizeof(ObjState),
-                                                      w.tc_xtra);
-}
-
+// The GN launchers: tile lists (n_tiles, tile_obj, tile_row0) and extras images are already in place, written by
+// the glue kernels in front (kernels_simt.cu: k_gn_sample / k_gn_rays / k_gn_prep / k_gn_solve).
 int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
-    int nl = 2;
-    if (w.phase == 0) { pack_extras_gn(w, st); ++nl; }   // the codes do not change between the phases of an iteration
-    k_tc_plan<<<1, 1024, 0, st>>>(w, 0);
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
     launch_tc<3>(a, sm_count, st);
-    return nl;
+    return 1;
 }
 
 int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
-    int nl = 2;
-    if (w.prm.pose_only) { pack_extras_gn(w, st); ++nl; }
-    k_tc_plan<<<1, 1024, 0, st>>>(w, 1);
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
     launch_tc<5>(a, sm_count, st);
-    return nl;
+    return 1;
 }
 
 }  // namespace dsp
