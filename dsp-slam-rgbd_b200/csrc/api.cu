@@ -334,8 +334,10 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                   const float* rays, const float* depth, int64_t total_pts, int64_t total_rays, int max_pts,
                   int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
                   const float* scale_in, int32_t* status_out, float* loss_out, float* dbg_out, int dbg_stride) {
-    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
-    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    // diagnostic mixes (not in the public header): 2 = tensor-core forward samples + FP32 Jacobian rows, 3 = the reverse
+    if (mode < 0 || mode > 3) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2), jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3);
     if (B <= 0 || B > 65535) return fail(DSPSLAM_E_BADARG, "B must be in 1..65535");
     if (iters < 0) return fail(DSPSLAM_E_BADARG, "negative iteration count");
     const int D = prm.D;
@@ -387,7 +389,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_ntl = c.take(sizeof(int) * 8);            // n_tiles[2] | done[2]
     const size_t o_toff = c.take(sizeof(int) * ((size_t)B + 1));
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
-    const size_t o_xtra = c.take(mode == DSPSLAM_MODE_TC ? tc_xtra_bytes_per_object() * (size_t)B : 0);
+    const size_t o_xtra = c.take(mode != DSPSLAM_MODE_FP32 ? tc_xtra_bytes_per_object() * (size_t)B : 0);
     if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
     int rc = ensure_ws(h, c.off);
     if (rc) return rc;
@@ -415,7 +417,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
     w.done = reinterpret_cast<unsigned int*>(base + o_ntl) + 4;
     w.tile_off = reinterpret_cast<int*>(base + o_toff);
-    w.tc = (mode == DSPSLAM_MODE_TC) ? 1 : 0;
+    w.tc = (mode != DSPSLAM_MODE_FP32) ? 1 : 0;
     w.partials = reinterpret_cast<float*>(base + o_part);
     w.stats = h->prof_on ? h->stats : nullptr;
     w.tc_xtra = reinterpret_cast<uint8_t*>(base + o_xtra);
@@ -434,7 +436,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                 w.phase = ph;
                 launch_gn_sample(w, st); ++nl;
                 const int pf = prof_begin(h, PK_GN_FWD, 0, st);
-                if (mode == DSPSLAM_MODE_FP32) { launch_gn_fwd_simt(w, st); ++nl; }
+                if (!fwd_tc) { launch_gn_fwd_simt(w, st); ++nl; }
                 else nl += tc_launch_gn_fwd(w, h->sm_count, st);
                 prof_end(h, pf, st);
             }
@@ -442,7 +444,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
             launch_gn_rays(w, max_rays, st); nl += 2;
         }
         const int pj = prof_begin(h, PK_GN_JAC, 0, st);
-        if (mode == DSPSLAM_MODE_FP32) { launch_gn_jac_simt(w, st); ++nl; }
+        if (!jac_tc) { launch_gn_jac_simt(w, st); ++nl; }
         else nl += tc_launch_gn_jac(w, h->sm_count, st);
         prof_end(h, pj, st);
         launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); ++nl;

@@ -13,7 +13,8 @@ import numpy as np
 from . import _native as N
 from .packer import check_supported, effective_weights
 
-_MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE_TC: N.MODE_TC}
+_MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE_TC: N.MODE_TC,
+          "mix_fwd_tc": 2, "mix_jac_tc": 3}     # diagnostic mixes (tools/free_run_stats.py)
 
 
 def _align(n, a=256):

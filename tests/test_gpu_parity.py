@@ -213,10 +213,16 @@ def test_reconstruct_object_api_free_run(mode, wfit):
         assert out.is_good and out.t_cam_obj.shape == (4, 4) and out.t_cam_obj.dtype == np.float32
         assert out.code.shape == (64,) and out.code.dtype == np.float32 and isinstance(out.loss, float)
         dt, ang, _ = synth.pose_errors(out.t_cam_obj, g["t_cam_obj"])
-        assert dt < 0.01 and ang < 1.0 and np.linalg.norm(out.code - g["code"]) < 0.05
+        # FP32 mode wanders by the reference's own noise floor (<= 0.1 deg here).  The tensor-core mode's 1e-4 SDF
+        # error is 1000x that perturbation: over 64 detections its end state sits 0.14 deg (median) / 1.4 deg (max)
+        # from the FP32 mode's (tools/free_run_stats.py) at the same final loss - the valley is flat along yaw/code.
+        if mode == "fp32":
+            assert dt < 0.01 and ang < 0.2 and np.linalg.norm(out.code - g["code"]) < 0.01
+        else:
+            assert dt < 0.02 and ang < 2.0 and np.linalg.norm(out.code - g["code"]) < 0.05
         assert abs(out.loss - float(g["loss"])) < 2e-2
         n_ok += (ang < 0.1)
-    assert n_ok >= (2 if mode == "fp32" else 1)
+    assert n_ok >= (4 if mode == "fp32" else 1)
 
 
 @pytest.mark.parametrize("mode", MODES)
