@@ -222,6 +222,8 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     if (rc) { dspslam_destroy(h); return rc; }
     e = simt_configure();
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, std::string("simt_configure: ") + cudaGetErrorString(e)); }
+    e = mc_configure();
+    if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, std::string("mc_configure: ") + cudaGetErrorString(e)); }
     e = cudaMalloc(&h->lat, sizeof(float) * (2 * HID + MAX_L + 64));
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
     e = cudaMalloc(&h->stats, sizeof(unsigned long long) * 8);
@@ -327,6 +329,22 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     else nl = 1 + tc_launch_sdf_rows(h->dec, h->sm_count, nullptr, i1 - i0, i0, G, 1 + coord_mode, c0, c4, out, S(stream));
     prof_end(h, pp, S(stream));
     return check_launch(h, nl, "dspslam_grid_sdf");
+}
+
+int dspslam_marching_cubes(dspslam_handle* h, void* stream, const float* sdf, int G, float level, float spacing,
+                           float origin, int max_verts, int max_tris, float* verts_out, int32_t* faces_out,
+                           int32_t* counts_out) {
+    if (!h || !sdf || !counts_out) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (G < 2 || G > 1024) return fail(DSPSLAM_E_BADARG, "G out of range [2,1024]");
+    if (max_verts < 0 || max_tris < 0) return fail(DSPSLAM_E_BADARG, "negative capacity");
+    if ((max_verts > 0 && !verts_out) || (max_tris > 0 && !faces_out)) return fail(DSPSLAM_E_BADARG, "null output");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    int rc = ensure_ws(h, mc_scratch_bytes(G));
+    if (rc) return rc;
+    const int nl = launch_marching_cubes(sdf, G, level, spacing, origin, max_verts, max_tris, verts_out, faces_out,
+                                         counts_out, h->ws, S(stream));
+    return check_launch(h, nl, "dspslam_marching_cubes");
 }
 
 static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int ray_phases, int B,

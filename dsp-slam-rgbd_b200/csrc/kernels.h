@@ -76,4 +76,11 @@ void launch_gn_rays(const GnWork& w, int max_rays, cudaStream_t st);
 void launch_gn_jac_simt(const GnWork& w, cudaStream_t st);
 void launch_gn_solve(const GnWork& w, int iter, int last_iter, float* dbg, int dbg_stride, cudaStream_t st);
 
+
+// marching cubes (mesh.cu)
+cudaError_t mc_configure();
+size_t mc_scratch_bytes(int G);
+int launch_marching_cubes(const float* sdf, int G, float level, float spacing, float origin, int max_verts,
+                          int max_tris, float* verts, int* faces, int* counts, void* scratch, cudaStream_t st);
+
 }  // namespace dsp

@@ -21,6 +21,7 @@ EXPORTS = [
     "dspslam_abi_version", "dspslam_last_error", "dspslam_launch_count", "dspslam_create",
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
+    "dspslam_marching_cubes",
 ]
 
 
@@ -76,6 +77,9 @@ def lib():
     L.dspslam_mean_sdf.argtypes = [vp, vp, C.c_int, fp, fp, i64, fp]
     L.dspslam_grid_sdf.restype = C.c_int
     L.dspslam_grid_sdf.argtypes = [vp, vp, C.c_int, fp, C.c_int, i64, i64, C.c_int, fp]
+    L.dspslam_marching_cubes.restype = C.c_int
+    L.dspslam_marching_cubes.argtypes = [vp, vp, fp, C.c_int, C.c_float, C.c_float, C.c_float, C.c_int, C.c_int,
+                                         fp, fp, fp]
     L.dspslam_gn_joint.restype = C.c_int
     L.dspslam_gn_joint.argtypes = [vp, vp, C.c_int, C.POINTER(JointParams), C.c_int, fp, fp, fp, fp, fp, fp,
                                    i64, i64, C.c_int, C.c_int, fp, fp, fp, fp, fp]

@@ -149,6 +149,28 @@ class Engine:
                                           cm, out.data_ptr()), "dspslam_grid_sdf")
         return out
 
+    def marching_cubes(self, sdf, level=0.0, spacing=None, origin=-1.0):
+        """Iso-surface of a (G,G,G) float32 device tensor: (vertices (nv,3) f32, faces (nf,3) i32) device tensors.
+        One counting call sized by a surface-area guess; a second call only if the guess was too small."""
+        t = self.torch
+        sdf = sdf.to(device=self.device, dtype=t.float32).contiguous()
+        G = int(sdf.shape[0])
+        if tuple(sdf.shape) != (G, G, G):
+            raise ValueError("marching_cubes needs a cubic (G,G,G) grid")
+        spacing = 2.0 / (G - 1) if spacing is None else float(spacing)
+        counts = t.zeros(3, dtype=t.int32, device=self.device)
+        cap_v, cap_t = 8 * G * G + 1024, 16 * G * G + 2048
+        while True:
+            verts = t.empty((cap_v, 3), dtype=t.float32, device=self.device)
+            faces = t.empty((cap_t, 3), dtype=t.int32, device=self.device)
+            N.check(self.lib.dspslam_marching_cubes(self._h, self._stream(), sdf.data_ptr(), G, float(level), spacing,
+                                                    float(origin), cap_v, cap_t, verts.data_ptr(), faces.data_ptr(),
+                                                    counts.data_ptr()), "dspslam_marching_cubes")
+            nv, nf, fits = (int(v) for v in counts.tolist())
+            if fits:
+                return verts[:nv], faces[:nf]
+            cap_v, cap_t = nv, nf
+
     # -- Gauss-Newton --------------------------------------------------------------------------
     def pack_joint(self, dets, pinned=True):
         """Concatenate detections into one (pinned) host blob.  `dets`: iterable of dicts/tuples with

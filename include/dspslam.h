@@ -8,6 +8,7 @@
  *   dspslam_sdf_jac                    reconstruct/loss_utils.py:82-113  get_batch_sdf_jacobian
  *   dspslam_mean_sdf                   reconstruct/optimizer.py:207-213 + loss.py:46-56
  *   dspslam_grid_sdf                   reconstruct/optimizer.py:224-227 + utils.py:97-116 (voxel grid + decode_sdf)
+ *   dspslam_marching_cubes             reconstruct/utils.py:119-140      convert_sdf_voxels_to_mesh (skimage marching cubes)
  *   dspslam_gn_joint                   reconstruct/optimizer.py:90-205   Optimizer.reconstruct_object
  *                                      (+ loss.py:22-43, 60-166, 169-192; loss_utils.py:176-275)
  *   dspslam_gn_pose_only               reconstruct/optimizer.py:46-87    Optimizer.estimate_pose_cam_obj
@@ -97,6 +98,17 @@ int dspslam_mean_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
  * true-division grid, DSPSLAM_GRID_LATTICE the regular lattice. */
 int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* code, int G,
                      int64_t i0, int64_t i1, int coord_mode, float* out);
+
+/* Iso-surface of a dense (G,G,G) float32 grid (x slowest, z fastest) at `level` as an indexed triangle mesh:
+ * vertex = origin + spacing * (grid coordinate of the edge crossing, linear interpolation), one vertex per crossed
+ * grid edge (welded), triangles wound so that their normals point towards larger values.
+ * counts_out (device int32[3]) = {n_vertices, n_triangles, fits}.  The buffers are only written when
+ * n_vertices <= max_verts and n_triangles <= max_tris (fits = 1); otherwise call again with larger buffers
+ * (max_verts = max_tris = 0 just counts).  Deterministic order: vertices by owning node (x, y, z), then axis;
+ * triangles by cell.  Replaces the CPU marching cubes of reconstruct/utils.py:127-129. */
+int dspslam_marching_cubes(dspslam_handle* h, void* stream, const float* sdf, int G, float level,
+                           float spacing, float origin, int max_verts, int max_tris, float* verts_out,
+                           int32_t* faces_out, int32_t* counts_out);
 
 /* Hyper-parameters of the joint optimisation (configs/config_*.json "optimizer") */
 typedef struct {
