@@ -141,6 +141,19 @@ def run_cpu_sample(n_obj, iters):
 def reference_arm(args, rank, world):
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm must use all host cores: re-run it in a child
+    # process without the thread caps (and without the rendezvous variables)
+    if world > 1 and not os.environ.get("DSPSLAM_REF_CHILD"):
+        env = {k: v for k, v in os.environ.items()
+               if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS", "RANK", "WORLD_SIZE",
+                            "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "MASTER_ADDR", "MASTER_PORT")}
+        env["DSPSLAM_REF_CHILD"] = "1"
+        sys.stdout.flush()
+        rc = subprocess.call([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--gpus", str(args.gpus),
+                              "--steps", str(args.steps), "--warmup", str(args.warmup)], env=env)
+        if rc != 0:
+            raise SystemExit(rc)
+        return
     # warm-up (BLAS thread pools, page-in) on a tiny case, then K bounded steps
     run_cpu_sample(1, 1)
     vals, secs = [], 0.0

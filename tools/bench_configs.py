@@ -1,0 +1,126 @@
+"""BASELINE.json configs other than the headline one (bench.py measures configs[1] = C2): one JSON line each.
+
+    python tools/bench_configs.py [c1] [c3] [c4] [c5]                                     (1 GPU)
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        tools/bench_configs.py c4 c5                                                      (N GPUs)
+
+  c1  single KITTI-style car through `Optimizer.reconstruct_object` (host arrays in/out): latency per call
+  c3  monocular, render-loss heavy: 16 detections x 256 surface pts + 1024 rays x 48 samples, 20 GN iterations
+  c4  mesh extraction: 256^3 grid SDF, slabs of the slowest axis per rank + NCCL all-gather, then marching cubes
+  c5  throughput sweep: 1024 C1-shaped detections partitioned contiguously across the ranks (no collective);
+      objects/s includes packing, H2D of the inputs and D2H of the results
+All times are device-synchronised wall times of the public API calls (max over ranks)."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path[:0] = [os.path.join(ROOT, "dsp-slam-rgbd_b200"), ROOT]
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+from dspslam import synth  # noqa: E402
+from dspslam.dist import grid_sdf_sharded, shard_range  # noqa: E402
+from reconstruct.optimizer import MeshExtractor, Optimizer  # noqa: E402
+
+rank = int(os.environ.get("RANK", 0))
+world = int(os.environ.get("WORLD_SIZE", 1))
+local = int(os.environ.get("LOCAL_RANK", 0))
+torch.cuda.set_device(local)
+if world > 1:
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+
+def sync():
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        torch.cuda.synchronize()
+
+
+def max_ranks(x):
+    if world == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def emit(**kw):
+    if rank == 0:
+        kw["n_gpus"] = world
+        print(json.dumps(kw), flush=True)
+
+
+def timed(fn, reps, warm=2):
+    for _ in range(warm):
+        fn()
+    sync()
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        out = fn()
+    torch.cuda.synchronize()
+    dt = max_ranks(time.perf_counter() - t0) / reps
+    sync()
+    return dt, out
+
+
+dec = synth.load_wfit()
+which = [a for a in sys.argv[1:] if a.startswith("c")] or ["c1", "c3", "c4", "c5"]
+
+if "c1" in which and world == 1:
+    opt = Optimizer(dec, synth.kitti_config(), mode="tc", device=local)
+    d = synth.make_kitti_detection(0)
+    dt, out = timed(lambda: opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"]), reps=20, warm=3)
+    emit(config="C1 single KITTI-style car: 250 surface pts + 450 rays x 50 samples, 10 GN iters, reconstruct_object()",
+         ms_per_object=dt * 1e3, objects_per_s=1.0 / dt, is_good=bool(out.is_good))
+
+if "c3" in which:
+    cfg = synth.redwood_config(iters=20, num_depth_samples=48)
+    opt = Optimizer(dec, cfg, mode="tc", device=local)
+    dets = [synth.make_mono_detection(rank * 16 + k) for k in range(16)]
+    dt, outs = timed(lambda: opt.reconstruct_objects(dets), reps=5)
+    emit(config="C3 monocular: 16 detections/GPU x 256 surface pts + 1024 rays x 48 samples, 20 GN iters, reconstruct_objects()",
+         ms_per_batch=dt * 1e3, objects_per_s=16 * world / dt, good=sum(1 for o in outs if o.is_good))
+
+if "c4" in which:
+    G = 256
+    ex = MeshExtractor(dec, 64, G, mode="tc", device=local)
+    code = np.zeros(64, np.float32)
+    code[:3] = [0.2, -0.1, 0.3]
+    dt_grid, vol = timed(lambda: grid_sdf_sharded(ex.engine, code, G, coord_mode="reference_shear"), reps=5)
+    if rank == 0:
+        for _ in range(2):
+            v, f = ex.engine.marching_cubes(vol)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        v, f = ex.engine.marching_cubes(vol)
+        torch.cuda.synchronize()
+        dt_mc = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        vh, fh = v.cpu().numpy(), f.cpu().numpy()
+        dt_d2h = time.perf_counter() - t0
+        emit(config="C4 mesh extraction: 256^3 grid SDF (x-slabs + all-gather) + marching cubes on rank 0",
+             ms_grid=dt_grid * 1e3, grid_mquery_per_s=G ** 3 / dt_grid / 1e6, grid_tflops=G ** 3 * 3.67104e6 / dt_grid / 1e12,
+             ms_marching_cubes=dt_mc * 1e3, ms_mesh_d2h=dt_d2h * 1e3, vertices=int(vh.shape[0]), faces=int(fh.shape[0]),
+             mc_gbps=(3 * 4 * G ** 3 + 16 * G ** 3) / dt_mc / 1e9)
+    sync()
+
+if "c5" in which:
+    n_total = 1024
+    lo, hi = shard_range(n_total, rank, world)
+    opt = Optimizer(dec, synth.kitti_config(), mode="tc", device=local)
+    dets = [synth.make_kitti_detection(k) for k in range(lo, hi)]
+    dt, outs = timed(lambda: opt.reconstruct_objects(dets), reps=3, warm=1)
+    good = sum(1 for o in outs if o.is_good)
+    if world > 1:
+        t = torch.tensor([good], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        good = int(t.item())
+    emit(config="C5 throughput sweep: 1024 C1-shaped detections split contiguously over the GPUs, H2D/D2H included",
+         seconds=dt, objects_per_s=n_total / dt, good=good)
+
+if world > 1:
+    dist.destroy_process_group()
