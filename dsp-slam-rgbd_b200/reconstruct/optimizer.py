@@ -11,7 +11,9 @@ Differences that are deliberate:
   * `loss` is a Python float (the reference returns a 0-d tensor; both cast to C++ float);
   * `estimate_pose_cam_obj` returns a float32 ndarray (the reference a CPU tensor; both cast to
     Eigen::Matrix4f through pybind11);
-  * additive batched entry points `reconstruct_objects` / `estimate_poses_cam_obj`;
+  * additive batched entry points `reconstruct_objects` / `estimate_poses_cam_obj`, and
+    `reconstruct_object_flip(s)`: the two-hypothesis call the mono path makes for objects that are not yet
+    initialised (`src/LocalMapping_util.cc:398-410`) as ONE batched launch sequence;
   * `mode="tc"` (tcgen05, FP16 operands) or `"fp32"` (validation mode) selects the arithmetic.
 """
 from __future__ import annotations
@@ -124,6 +126,39 @@ class Optimizer(object):
         if debug:
             return outs, res
         return outs
+
+    # ---- orientation disambiguation, src/LocalMapping_util.cc:398-410 ---------------------------
+    @staticmethod
+    def flipped(t_cam_obj):
+        """The second hypothesis of the mono path: object x and z axes negated (a half turn about the
+        object's y axis).  `flipped_Two.col(0) *= -1; col(2) *= -1` and `SE3Tcw * flipped_Two` commute with
+        the left factor, so the flip acts on the columns of `t_cam_obj` directly."""
+        T = np.array(t_cam_obj, dtype=np.float32, copy=True)
+        T[:, 0] *= -1
+        T[:, 2] *= -1
+        return T
+
+    def reconstruct_object_flip(self, t_cam_obj, pts, rays, depth, code=None):
+        """`reconstruct_object` on the pose and on its flipped twin in one batch; returns the result the
+        reference's C++ keeps: the first one unless its loss is strictly greater than the flipped one's
+        (`src/LocalMapping_util.cc:407-408`)."""
+        return self.reconstruct_objects_flip([(t_cam_obj, pts, rays, depth, code)])[0]
+
+    def reconstruct_objects_flip(self, detections, return_both=False):
+        """Batched two-hypothesis reconstruction: 2B objects in one launch sequence."""
+        dets = []
+        for d in detections:
+            if isinstance(d, dict):
+                d = (d["t_cam_obj"], d["pts"], d["rays"], d["depth"], d.get("code"))
+            code = d[4] if len(d) > 4 else None
+            dets.append((d[0], d[1], d[2], d[3], code))
+            dets.append((self.flipped(d[0]), d[1], d[2], d[3], code))
+        outs = self.reconstruct_objects(dets)
+        if return_both:
+            return [(outs[2 * i], outs[2 * i + 1]) for i in range(len(outs) // 2)]
+        # NaN losses compare False, exactly as the C++ `>` on floats does
+        return [outs[2 * i + 1] if outs[2 * i].loss > outs[2 * i + 1].loss else outs[2 * i]
+                for i in range(len(outs) // 2)]
 
     # ---- optimizer.py:207-213 ---------------------------------------------------------------------
     def compute_sdf_loss_objectpoint_zhjd(self, pts_surface_obj, code):
