@@ -10,6 +10,7 @@
 #include "../../include/dspslam.h"
 #include "kernels.h"
 #include "kernels_tc.h"
+#include "frame.h"
 
 using namespace dsp;
 
@@ -513,6 +514,73 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
     return gn_run(h, stream, mode, prm, num_iterations, 1, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
                   total_pts, 0, max_pts, 0, t_co_se3_io, t_co_se3_io, code, nullptr, scale, nullptr, nullptr, dbg_out,
                   64);
+}
+
+static int frame_params(const dspslam_frame_params* p, FrameParamsDev& d) {
+    if (p->img_w <= 0 || p->img_h <= 0 || p->num_lidar_max <= 0 || p->downsample_ratio <= 0 || p->max_background < 0 ||
+        p->max_background > 1024)
+        return fail(DSPSLAM_E_BADARG, "frame parameters out of range");
+    d.img_w = p->img_w; d.img_h = p->img_h; d.max_pts = p->num_lidar_max; d.min_mask_area = p->min_mask_area;
+    d.alpha = p->downsample_ratio; d.max_bg = p->max_background;
+    memcpy(d.K, p->K, sizeof d.K);
+    memcpy(d.invK, p->invK, sizeof d.invK);
+    for (int i = 0; i < 3; ++i) {
+        for (int j = 0; j < 3; ++j) d.Rcv[3 * i + j] = p->T_cam_velo[4 * i + j];
+        d.tcv[i] = p->T_cam_velo[4 * i + 3];
+    }
+    d.k1 = p->k1; d.k2 = p->k2;
+    memcpy(d.Kd, p->K64, sizeof d.Kd);
+    memcpy(d.invKd, p->invK64, sizeof d.invKd);
+    return 0;
+}
+
+int dspslam_frame_build_kitti(dspslam_handle* h, void* stream, const dspslam_frame_params* prm, const float* velo,
+                              int64_t n_velo, const dspslam_frame_box* boxes_host, int B, const uint8_t* masks,
+                              int n_masks, const float* bboxes, int32_t* pts_off, int32_t* ray_off, int32_t* n_fg,
+                              float* pts, float* rays, float* depth, int32_t* info) {
+    if (!h || !prm || !boxes_host || !pts_off || !ray_off || !n_fg || !pts || !rays || !depth || !info)
+        return fail(DSPSLAM_E_BADARG, "null argument");
+    if (B <= 0 || B > FB_MAX_DETS) return fail(DSPSLAM_E_BADARG, "B out of range [1,256]");
+    if (n_velo < 0 || (n_velo > 0 && !velo)) return fail(DSPSLAM_E_BADARG, "bad scan");
+    if (n_masks < 0 || n_masks > FB_MAX_MASKS || (n_masks > 0 && (!masks || !bboxes)))
+        return fail(DSPSLAM_E_BADARG, "n_masks out of range [0,256] or null masks");
+    if ((reinterpret_cast<uintptr_t>(velo) & 15) != 0) return fail(DSPSLAM_E_BADARG, "scan must be 16-byte aligned");
+    FrameParamsDev d{};
+    int rc = frame_params(prm, d);
+    if (rc) return rc;
+    std::vector<FrameBoxDev> bx((size_t)B);
+    std::vector<int> front((size_t)B);
+    for (int i = 0; i < B; ++i) {
+        const dspslam_frame_box& s = boxes_host[i];
+        for (int r = 0; r < 3; ++r) {
+            for (int c = 0; c < 3; ++c) bx[i].Rov[3 * r + c] = s.T_obj_velo[4 * r + c];
+            bx[i].tov[r] = s.T_obj_velo[4 * r + 3];
+            bx[i].lo[r] = s.lo[r]; bx[i].hi[r] = s.hi[r]; bx[i].half[r] = s.half[r];
+        }
+        front[i] = s.is_front;
+    }
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    rc = ensure_ws(h, frame_scratch_bytes(n_velo, B, n_masks, d.max_bg));
+    if (rc) return rc;
+    const int nl = launch_frame_kitti(d, velo, n_velo, bx.data(), front.data(), B, masks, n_masks, bboxes, pts_off,
+                                      ray_off, n_fg, pts, rays, depth, info, h->ws, S(stream));
+    return check_launch(h, nl, "dspslam_frame_build_kitti");
+}
+
+int dspslam_frame_build_mono(dspslam_handle* h, void* stream, const dspslam_frame_params* prm, const uint8_t* masks,
+                             int n_masks, const float* bboxes, float* rays_out, int32_t* info_out) {
+    if (!h || !prm || !masks || !bboxes || !rays_out || !info_out) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (n_masks <= 0 || n_masks > FB_MAX_MASKS) return fail(DSPSLAM_E_BADARG, "n_masks out of range [1,256]");
+    FrameParamsDev d{};
+    int rc = frame_params(prm, d);
+    if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    rc = ensure_ws(h, frame_scratch_bytes(0, 1, n_masks, d.max_bg));
+    if (rc) return rc;
+    const int nl = launch_frame_mono(d, masks, n_masks, bboxes, rays_out, info_out, h->ws, S(stream));
+    return check_launch(h, nl, "dspslam_frame_build_mono");
 }
 
 int dspslam_profile_enable(dspslam_handle* h, int on) {

@@ -21,8 +21,11 @@ EXPORTS = [
     "dspslam_abi_version", "dspslam_last_error", "dspslam_launch_count", "dspslam_create",
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
-    "dspslam_marching_cubes",
+    "dspslam_marching_cubes", "dspslam_frame_build_kitti", "dspslam_frame_build_mono",
 ]
+FRAME_INFO = 8
+FRAME_MAX_DETS = 256
+FRAME_MAX_MASKS = 256
 
 
 class DecoderDesc(C.Structure):
@@ -41,6 +44,18 @@ class Profile(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("ms_gn_fwd", "ms_gn_jac", "ms_rows_fwd", "ms_rows_jac")] + \
                [(n, C.c_int64) for n in ("rows_gn_fwd", "rows_gn_jac", "rows_fwd", "rows_jac",
                                          "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac", "rows_gn_inball")]
+
+
+class FrameParams(C.Structure):
+    _fields_ = [("img_w", C.c_int32), ("img_h", C.c_int32), ("num_lidar_max", C.c_int32),
+                ("min_mask_area", C.c_int32), ("downsample_ratio", C.c_int32), ("max_background", C.c_int32),
+                ("K", C.c_float * 9), ("invK", C.c_float * 9), ("T_cam_velo", C.c_float * 12),
+                ("k1", C.c_double), ("k2", C.c_double), ("K64", C.c_double * 9), ("invK64", C.c_double * 9)]
+
+
+class FrameBox(C.Structure):
+    _fields_ = [("T_obj_velo", C.c_float * 12), ("lo", C.c_float * 3), ("hi", C.c_float * 3),
+                ("half", C.c_float * 3), ("is_front", C.c_int32)]
 
 
 class NativeError(RuntimeError):
@@ -89,6 +104,11 @@ def lib():
     L.dspslam_profile_enable.argtypes = [vp, C.c_int]
     L.dspslam_profile_read.restype = C.c_int
     L.dspslam_profile_read.argtypes = [vp, C.POINTER(Profile)]
+    L.dspslam_frame_build_kitti.restype = C.c_int
+    L.dspslam_frame_build_kitti.argtypes = [vp, vp, C.POINTER(FrameParams), fp, i64, C.POINTER(FrameBox), C.c_int,
+                                            fp, C.c_int, fp, fp, fp, fp, fp, fp, fp, fp]
+    L.dspslam_frame_build_mono.restype = C.c_int
+    L.dspslam_frame_build_mono.argtypes = [vp, vp, C.POINTER(FrameParams), fp, C.c_int, fp, fp, fp]
     if L.dspslam_abi_version() != ABI_VERSION:
         raise NativeError("libdspslam_sm100.so ABI version mismatch")
     _lib = L

@@ -127,6 +127,8 @@ def _cfg(data_type, voxels_dim, k1, k2, k3, k4, b1, b2, iters, s_damp,
     from reconstruct.utils import ForceKeyErrorDict
     d = dict(
         data_type=data_type, voxels_dim=voxels_dim, DeepSDF_DIR="",
+        # detection association (configs/config_kitti.json:14-18; the mono configs share the first three)
+        min_bb_area=1600, min_mask_area=1000, downsample_ratio=4.0, num_lidar_max=250, num_lidar_min=10,
         optimizer=dict(
             code_len=CODE_LEN, num_depth_samples=num_depth_samples,
             cut_off_threshold=0.01,

@@ -127,6 +127,26 @@ class Optimizer(object):
             return outs, res
         return outs
 
+    # ---- a whole frame, reconstruct_frame.py:45-57 ---------------------------------------------------
+    def reconstruct_frame(self, frame_batch, debug=False):
+        """Joint optimisation of every detection of a `dspslam.frame.FrameBatch` (built on the device by
+        `FrameBuilder.build_kitti`): the loop of `reconstruct_frame.py:45-57` as one launch sequence on data that
+        never left HBM.  Returns one result per detection in depth order; detections the reference skips
+        (`det.rays is None`) come back with `is_good=False`."""
+        fb = frame_batch
+        if fb.total_rays == 0 or fb.total_pts == 0:
+            return [ForceKeyErrorDict(t_cam_obj=None, code=None, is_good=False, loss=float("nan")) for _ in range(fb.B)]
+        dbg = self.engine.run_joint(fb, self._params(), mode=self.mode, debug=debug)
+        res = self.engine.download_joint(fb, dbg)
+        outs = []
+        for b in range(fb.B):
+            if res.status[b] == 0 and fb.info[b, 4]:
+                outs.append(ForceKeyErrorDict(t_cam_obj=res.t_cam_obj[b].copy(), code=res.code[b, : self.code_len].copy(),
+                                              is_good=True, loss=float(res.loss[b])))
+            else:
+                outs.append(ForceKeyErrorDict(t_cam_obj=None, code=None, is_good=False, loss=float(res.loss[b])))
+        return (outs, res) if debug else outs
+
     # ---- orientation disambiguation, src/LocalMapping_util.cc:398-410 ---------------------------
     @staticmethod
     def flipped(t_cam_obj):

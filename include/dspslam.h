@@ -13,6 +13,10 @@
  *                                      (+ loss.py:22-43, 60-166, 169-192; loss_utils.py:176-275)
  *   dspslam_gn_pose_only               reconstruct/optimizer.py:46-87    Optimizer.estimate_pose_cam_obj
  *   dspslam_profile_enable / _read     reconstruct/loss_utils.py:278-283 get_time (the reference's only timing hook)
+ *   dspslam_frame_build_kitti          reconstruct/kitti_sequence.py:136-155,180-209 (+ :70-97, loss_utils.py:23-37)
+ *                                      FrameWithLiDAR.get_detections: LiDAR crop, sub-sampling, mask association,
+ *                                      background pixels, rays - output in the batch layout of dspslam_gn_joint
+ *   dspslam_frame_build_mono           reconstruct/mono_sequence.py:95-106  background rays of the largest mask
  *
  * Conventions
  *   - plain C types only; all array arguments are DEVICE pointers unless the name
@@ -168,6 +172,50 @@ typedef struct {
 } dspslam_profile;
 int dspslam_profile_enable(dspslam_handle* h, int on);
 int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out);
+
+/* ---- detection -> optimiser-input builder (the step in front of the GN loop) ----------------------------------
+ * Bit-identical to the reference's numpy (FP32 / FP64 evaluation order reproduced, stable compaction). */
+typedef struct {
+    int32_t img_w, img_h;
+    int32_t num_lidar_max;    /* configs.num_lidar_max: surface points kept per detection (kitti_sequence.py:149-151) */
+    int32_t min_mask_area;    /* configs.min_mask_area (kitti_sequence.py:196)                                       */
+    int32_t downsample_ratio; /* int(configs.downsample_ratio): lattice stride of pixels_sampler (:71)              */
+    int32_t max_background;   /* 200 background pixels per detection (:199-201), <= 1024                            */
+    float K[9], invK[9];      /* camera intrinsics and their inverse, row-major (sequence.K_cam / invK_cam)         */
+    float T_cam_velo[12];     /* first three rows of the velodyne->camera transform, row-major                      */
+    double k1, k2;            /* radial distortion of the monocular camera (mono_sequence.py:103)                   */
+    double K64[9], invK64[9]; /* monocular path: MonoSequence keeps FP64 intrinsics (mono_sequence.py:130-131)      */
+} dspslam_frame_params;
+
+/* Per-detection 4x4 bookkeeping done by the host mirror exactly as the reference does it in numpy
+ * (kitti_sequence.py:125-135,141-143,163): inverse box pose, 3 m cube, half extents (w,l enlarged by 1.1). */
+typedef struct {
+    float T_obj_velo[12]; /* first three rows, row-major */
+    float lo[3], hi[3];   /* trans -/+ 3 m                */
+    float half[3];        /* (1.1 w/2, h/2, 1.1 l/2)     */
+    int32_t is_front;     /* T_cam_obj[2,3] > 0          */
+} dspslam_frame_box;
+
+#define DSPSLAM_FRAME_INFO 8 /* int32 per detection: n_in_box, M, n_in_fov, mask_id (-1 none), has_rays, n_bg, hits, 0 */
+#define DSPSLAM_FRAME_MAX_DETS 256
+#define DSPSLAM_FRAME_MAX_MASKS 256
+
+/* One KITTI stereo+LiDAR frame: B detections (depth order, boxes_host) against the scan velo[n_velo][4] and the
+ * 2-D instance masks masks[n_masks][img_h][img_w] (bytes, non-zero = on) / bboxes[n_masks][4] (l,t,r,b).
+ * Outputs (device, capacities: pts 3*B*num_lidar_max floats, rays 3*B*(num_lidar_max+max_background),
+ * depth B*(num_lidar_max+max_background)) are the pts_off / ray_off / n_fg / pts / rays / depth arguments of
+ * dspslam_gn_joint; detections without rays (not in front, no mask, mask too small) keep their surface points
+ * and get zero rays.  info[B][DSPSLAM_FRAME_INFO]. */
+int dspslam_frame_build_kitti(dspslam_handle* h, void* stream, const dspslam_frame_params* prm,
+                              const float* velo, int64_t n_velo, const dspslam_frame_box* boxes_host, int B,
+                              const uint8_t* masks, int n_masks, const float* bboxes,
+                              int32_t* pts_off, int32_t* ray_off, int32_t* n_fg, float* pts, float* rays,
+                              float* depth, int32_t* info);
+
+/* Monocular frame: background rays of the largest mask (rays_out[max_background][3]); info_out[2] = {mask_id, n_bg}. */
+int dspslam_frame_build_mono(dspslam_handle* h, void* stream, const dspslam_frame_params* prm,
+                             const uint8_t* masks, int n_masks, const float* bboxes, float* rays_out,
+                             int32_t* info_out);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,210 @@
+"""Detection -> optimiser-input builder: reconstruct/kitti_sequence.py:112-216 and
+mono_sequence.py:80-114.
+
+CPU tests pin the numpy oracle to golden vectors produced by the reference's own classes
+(oracle/make_frame_goldens.py); GPU tests require the CUDA builder (csrc/frame.cu, through the C ABI) to be
+BIT-IDENTICAL to those vectors - this is index / byte work - and check the frame -> Gauss-Newton hand-over on
+the device against the host path."""
+import ast
+import os
+
+import numpy as np
+import pytest
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+G = os.path.join(ROOT, "tests", "golden")
+KITTI = [0, 1, 2]
+
+
+def load(name):
+    with np.load(os.path.join(G, name)) as z:
+        return {k: z[k] for k in z.files}
+
+
+def frame(seed):
+    from dspslam.frame_synth import synth_kitti_frame
+    g = load("frame_kitti_%d.npz" % seed)
+    return g, synth_kitti_frame(seed, **ast.literal_eval(str(g["kw"])))
+
+
+def check_instances(inst, g, get):
+    assert len(inst) == int(g["n_inst"])
+    for i, ins in enumerate(inst):
+        assert np.array_equal(get(ins, "T_cam_obj"), g["i%d_T_cam_obj" % i])
+        assert np.array_equal(get(ins, "surface_points"), g["i%d_pts" % i])
+        assert bool(get(ins, "is_front")) == bool(g["i%d_is_front" % i])
+        rays = get(ins, "rays")
+        assert (rays is not None) == bool(g["i%d_has_rays" % i])
+        if rays is not None:
+            assert np.array_equal(rays, g["i%d_rays" % i])
+            assert np.array_equal(get(ins, "depth"), g["i%d_depth" % i])
+
+
+# ---- CPU: oracle against the reference's vectors ---------------------------------------------------------------
+@pytest.mark.parametrize("seed", KITTI)
+def test_oracle_kitti_frame_vs_reference_golden(seed):
+    from dspslam.frame_synth import IMG_H, IMG_W, K, T_CAM_VELO
+    from oracle import frame_oracle as fo
+    g, (scan, boxes, masks, bbs) = frame(seed)
+    inst = fo.kitti_frame(scan, boxes, masks, bbs, K, np.linalg.inv(K).astype(np.float32), T_CAM_VELO, IMG_W, IMG_H)
+    check_instances(inst, g, lambda ins, k: ins[k])
+    for i, ins in enumerate(inst):
+        assert ins["mask_id"] == int(g["i%d_mask_id" % i])
+
+
+@pytest.mark.parametrize("seed", [0, 1])
+def test_oracle_mono_background_rays_vs_reference_golden(seed):
+    from dspslam.frame_synth import IMG_H, IMG_W, synth_kitti_frame
+    from oracle import frame_oracle as fo
+    g = load("frame_mono_%d.npz" % seed)
+    _, _, masks, bbs = synth_kitti_frame(int(g["seed"]), n_cars=3, n_ground=10)
+    n, rays = fo.mono_background_rays(masks, bbs, g["K"], np.linalg.inv(g["K"]), float(g["k1"]), float(g["k2"]),
+                                      IMG_W, IMG_H)
+    assert n == int(g["mask_id"]) and np.array_equal(rays, g["background_rays"])
+
+
+def test_linspace_restatement_matches_numpy():
+    from oracle import frame_oracle as fo
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        a, n = int(rng.integers(0, 50)), int(rng.integers(1, 400))
+        b = a + int(rng.integers(0, 5000))
+        assert np.array_equal(fo.linspace_int(a, b, n), np.linspace(a, b, n).astype(np.int32))
+
+
+def test_undistort_restatement_known_answers():
+    """No distortion is the identity; the fixed point satisfies the forward radial model to ~1e-3 pixel."""
+    from oracle import frame_oracle as fo
+    K = np.array([[535.4, 0, 320.1], [0, 539.2, 247.6], [0, 0, 1]])
+    pix = np.array([[10, 20], [320, 240], [600, 400]], np.float32)
+    assert np.allclose(fo.undistort_points(pix, K, 0.0, 0.0), pix, atol=1e-4)
+    und = fo.undistort_points(pix, K, -0.1, 0.02).astype(np.float64)
+    x, y = (und[:, 0] - K[0, 2]) / K[0, 0], (und[:, 1] - K[1, 2]) / K[1, 1]
+    r2 = x * x + y * y
+    f = 1 + (-0.1) * r2 + 0.02 * r2 * r2
+    assert np.allclose(np.stack([x * f * K[0, 0] + K[0, 2], y * f * K[1, 1] + K[1, 2]], 1), pix, atol=5e-3)
+
+
+# ---- GPU: the CUDA builder, bit-exact -----------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def eng():
+    from dspslam import synth
+    from dspslam.engine import Engine
+    return Engine(synth.load_wfit())
+
+
+def _builder(eng, **kw):
+    from dspslam.frame import FrameBuilder
+    from dspslam.frame_synth import IMG_H, IMG_W, K, T_CAM_VELO
+    return FrameBuilder(eng, K, np.linalg.inv(K).astype(np.float32), T_CAM_VELO, IMG_W, IMG_H, **kw)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", KITTI)
+def test_gpu_kitti_frame_bit_exact_vs_reference_golden(seed, eng):
+    g, (scan, boxes, masks, bbs) = frame(seed)
+    b = _builder(eng)
+    fb = b.build_kitti(scan, boxes, masks, bbs)
+    inst = b.instances(fb, masks, bbs)
+    check_instances(inst, g, lambda ins, k: ins[k])
+    for i, ins in enumerate(inst):
+        assert int(fb.info[i, 3]) == int(g["i%d_mask_id" % i])
+        assert ins.num_surface_points == g["i%d_pts" % i].shape[0]
+    # packed layout invariants of the dspslam_gn_joint hand-over
+    assert fb.pts_off[0] == 0 and fb.ray_off[0] == 0
+    assert np.all(np.diff(fb.pts_off) == fb.info[:, 1])
+    assert np.all(np.diff(fb.ray_off) == np.where(fb.info[:, 4] > 0, fb.info[:, 1] + fb.info[:, 5], 0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cfg", [dict(num_lidar_max=1), dict(num_lidar_max=7, max_background=3, downsample_ratio=1.0),
+                                 dict(num_lidar_max=100000, max_background=1024, downsample_ratio=2.0),
+                                 dict(num_lidar_max=64, min_mask_area=10 ** 7)])
+def test_gpu_kitti_frame_vs_oracle_edge_configs(cfg, eng):
+    """Sub-sampling caps of 1 / tiny / never reached, every lattice pixel (stride 1), masks all too small."""
+    from dspslam.frame_synth import IMG_H, IMG_W, K, T_CAM_VELO, synth_kitti_frame
+    from oracle import frame_oracle as fo
+    scan, boxes, masks, bbs = synth_kitti_frame(5, n_cars=4, n_ground=30000, pts_per_car=900)
+    ref = fo.kitti_frame(scan, boxes, masks, bbs, K, np.linalg.inv(K).astype(np.float32), T_CAM_VELO, IMG_W, IMG_H,
+                         num_lidar_max=cfg.get("num_lidar_max", 250), min_mask_area=cfg.get("min_mask_area", 1000),
+                         downsample_ratio=cfg.get("downsample_ratio", 4.0), max_bg=cfg.get("max_background", 200))
+    b = _builder(eng, **cfg)
+    inst = b.instances(b.build_kitti(scan, boxes, masks, bbs))
+    assert len(inst) == len(ref)
+    for a, r in zip(inst, ref):
+        assert np.array_equal(a.surface_points, r["surface_points"])
+        assert (a.rays is None) == (r["rays"] is None)
+        if a.rays is not None:
+            assert np.array_equal(a.rays, r["rays"]) and np.array_equal(a.depth, r["depth"])
+
+
+@pytest.mark.gpu
+def test_gpu_frame_empty_inputs(eng):
+    """No LiDAR points, no masks: detections keep zero points / no rays (kitti_sequence.py:173-174)."""
+    from dspslam.frame_synth import synth_kitti_frame
+    scan, boxes, masks, bbs = synth_kitti_frame(6, n_cars=2, n_ground=2000)
+    b = _builder(eng)
+    fb = b.build_kitti(scan, boxes, masks[:0], bbs[:0])
+    assert np.all(fb.info[:, 3] == -1) and fb.total_rays == 0 and fb.total_pts > 0
+    fb = b.build_kitti(scan[:0], boxes, masks, bbs)
+    assert fb.total_pts == 0 and fb.total_rays == 0
+    # more than 32 detections: the crop kernels run in groups of 32 boxes
+    many = np.concatenate([boxes] * 13)[:37]
+    fb = b.build_kitti(scan, many, masks, bbs)
+    inst = b.instances(fb)
+    one = b.instances(b.build_kitti(scan, boxes, masks, bbs))
+    assert len(inst) == 37 and fb.info[:, 1].sum() == fb.total_pts
+    for i in inst:                           # every copy equals the instance of the box it duplicates
+        src = [o for o in one if np.array_equal(o.T_cam_obj, i.T_cam_obj)]
+        assert len(src) == 1 and np.array_equal(i.surface_points, src[0].surface_points)
+        assert (i.rays is None) == (src[0].rays is None)
+        if i.rays is not None:
+            assert np.array_equal(i.rays, src[0].rays)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("seed", [0, 1])
+def test_gpu_mono_background_rays_bit_exact_vs_reference_golden(seed, eng):
+    from dspslam.frame import FrameBuilder
+    from dspslam.frame_synth import IMG_H, IMG_W, synth_kitti_frame
+    g = load("frame_mono_%d.npz" % seed)
+    _, _, masks, bbs = synth_kitti_frame(int(g["seed"]), n_cars=3, n_ground=10)
+    b = FrameBuilder(eng, g["K"], None, None, IMG_W, IMG_H, k1=float(g["k1"]), k2=float(g["k2"]))
+    mid, rays = b.background_rays_mono(masks, bbs)
+    assert mid == int(g["mask_id"]) and np.array_equal(rays, g["background_rays"])
+
+
+@pytest.mark.gpu
+def test_gpu_frame_to_gauss_newton_on_device(eng):
+    """The device-resident hand-over: reconstruct_frame(FrameBatch) == reconstruct_objects(host copies of the same
+    detections), and the reference-shaped sequence mirror returns the same instances."""
+    import types
+    from dspslam import synth
+    from dspslam.frame_synth import K, T_CAM_VELO
+    from reconstruct.kitti_sequence import FrameWithLiDAR
+    from reconstruct.optimizer import Optimizer
+    g, (scan, boxes, masks, bbs) = frame(2)
+    cfg = synth.kitti_config()
+    cfg.optimizer.joint_optim.num_iterations = 2
+    opt = Optimizer(synth.load_wfit(), cfg, mode="fp32")
+    b = _builder(opt.engine)
+    fb = b.build_kitti(scan, boxes, masks, bbs)
+    inst = b.instances(fb)
+    outs = opt.reconstruct_frame(fb)
+    assert len(outs) == fb.B
+    dets = [(i.T_cam_obj, i.surface_points, i.rays, i.depth) for i in inst if i.rays is not None]
+    refs = iter(opt.reconstruct_objects(dets))
+    for i, o in zip(inst, outs):
+        if i.rays is None:
+            assert not o.is_good
+            continue
+        r = next(refs)
+        assert o.is_good == r.is_good
+        if o.is_good:
+            assert np.allclose(o.t_cam_obj, r.t_cam_obj, atol=1e-5) and np.allclose(o.code, r.code, atol=1e-5)
+    # the reference-shaped mirror (arrays instead of files)
+    seq = types.SimpleNamespace(configs=synth.kitti_config(), K_cam=K, invK_cam=np.linalg.inv(K).astype(np.float32),
+                                T_cam_velo=T_CAM_VELO, engine=opt.engine)
+    fr = FrameWithLiDAR(seq, 0, velo_pts=scan, detections_3d=boxes, det_2d={"pred_masks": masks, "pred_boxes": bbs})
+    fr.get_detections()
+    check_instances(fr.instances, g, lambda ins, k: ins[k])
