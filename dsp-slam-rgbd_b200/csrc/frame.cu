@@ -22,7 +22,7 @@ namespace dsp {
 namespace {
 
 constexpr int FB_THREADS = 256;
-constexpr int FB_SUB = 4;                          // sub-rows of FB_THREADS consecutive points per chunk
+constexpr int FB_SUB = 1;                          // sub-rows of FB_THREADS consecutive points per chunk
 constexpr int FB_CHUNK = FB_THREADS * FB_SUB;      // points per CTA
 constexpr int FB_WARPS = FB_THREADS / 32;
 
@@ -116,19 +116,16 @@ k_fb_count(const float4* __restrict__ velo, int64_t n, const __grid_constant__ F
     if (tid < bx.n) chunk_cnt[(size_t)(d0 + tid) * n_chunks + blockIdx.x] = s_cnt[tid];
 }
 
-// ---- 2. exclusive scan of the chunk counts per detection, point offsets of the packed output ------------------
+// ---- 2. exclusive scan of the chunk counts per detection (one warp each), point offsets of the packed output ---
 __global__ void __launch_bounds__(1024)
 k_fb_scan(const int* __restrict__ chunk_cnt, int* __restrict__ chunk_off, int n_chunks, int B, int cap,
           int* __restrict__ pts_off, int* __restrict__ info) {
-    __shared__ int s_warp[32];
-    __shared__ int s_run;
+    __shared__ int s_tot[FB_MAX_DETS];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    int off = 0;
-    for (int d = 0; d < B; ++d) {
-        if (tid == 0) s_run = 0;
-        __syncthreads();
-        for (int base = 0; base < n_chunks; base += 1024) {
-            const int c = base + tid;
+    for (int d = warp; d < B; d += 32) {
+        int run = 0;
+        for (int base = 0; base < n_chunks; base += 32) {
+            const int c = base + lane;
             const int v = c < n_chunks ? chunk_cnt[(size_t)d * n_chunks + c] : 0;
             int inc = v;
 #pragma unroll
@@ -136,35 +133,24 @@ k_fb_scan(const int* __restrict__ chunk_cnt, int* __restrict__ chunk_off, int n_
                 const int t = __shfl_up_sync(0xffffffffu, inc, s);
                 if (lane >= s) inc += t;
             }
-            if (lane == 31) s_warp[warp] = inc;
-            __syncthreads();
-            if (warp == 0) {
-                int w = s_warp[lane];
-#pragma unroll
-                for (int s = 1; s < 32; s <<= 1) {
-                    const int t = __shfl_up_sync(0xffffffffu, w, s);
-                    if (lane >= s) w += t;
-                }
-                s_warp[lane] = w;
-            }
-            __syncthreads();
-            const int run = s_run;
-            const int excl = run + (warp ? s_warp[warp - 1] : 0) + inc - v;
-            if (c < n_chunks) chunk_off[(size_t)d * n_chunks + c] = excl;
-            __syncthreads();
-            if (tid == 1023) s_run = run + s_warp[31];
-            __syncthreads();
+            if (c < n_chunks) chunk_off[(size_t)d * n_chunks + c] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
         }
-        if (tid == 0) {
-            const int N = s_run;
-            info[d * FB_INFO + FBI_IN_BOX] = N;
-            info[d * FB_INFO + FBI_M] = N < cap ? N : cap;
-            pts_off[d] = off;
+        if (lane == 0) {
+            s_tot[d] = run;
+            info[d * FB_INFO + FBI_IN_BOX] = run;
+            info[d * FB_INFO + FBI_M] = run < cap ? run : cap;
         }
-        off += (s_run < cap ? s_run : cap);
-        __syncthreads();
     }
-    if (tid == 0) pts_off[B] = off;
+    __syncthreads();
+    if (tid == 0) {
+        int off = 0;
+        for (int d = 0; d < B; ++d) {
+            pts_off[d] = off;
+            off += s_tot[d] < cap ? s_tot[d] : cap;
+        }
+        pts_off[B] = off;
+    }
 }
 
 // ---- 3. stable compaction + linspace sub-sampling + camera-frame transform -------------------------------------
@@ -221,12 +207,26 @@ k_fb_emit(const float4* __restrict__ velo, int64_t n, const __grid_constant__ Fr
     }
 }
 
-// ---- 4. mask areas ------------------------------------------------------------------------------------------------
+// ---- 4. mask areas (bytes are 0/1 or 0/255: count the non-zero ones, four per 32-bit load) -----------------------
 __global__ void __launch_bounds__(FB_THREADS)
 k_fb_mask_area(const uint8_t* __restrict__ masks, int hw, int* __restrict__ area) {
     const uint8_t* mk = masks + (size_t)blockIdx.y * hw;
+    const int head = (int)((4 - (reinterpret_cast<uintptr_t>(mk) & 3)) & 3);       // bytes before the first aligned word
+    const int n_words = hw > head ? (hw - head) / 4 : 0;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(mk + head);
     int c = 0;
-    for (int i = blockIdx.x * FB_THREADS + threadIdx.x; i < hw; i += gridDim.x * FB_THREADS) c += mk[i] != 0;
+    const int t = blockIdx.x * FB_THREADS + threadIdx.x, stride = gridDim.x * FB_THREADS;
+    for (int i = t; i < n_words; i += stride) {
+        const uint32_t v = __ldg(w + i);
+        // per byte: non-zero -> 1.  (v | v>>4) folds nibbles, then |>>2, |>>1 fold into bit 0 of every byte
+        uint32_t f = v | (v >> 4);
+        f |= f >> 2;
+        f |= f >> 1;
+        c += __popc(f & 0x01010101u);
+    }
+    if (t < head && t < hw) c += mk[t] != 0;
+    const int tail0 = head + 4 * n_words;
+    if (t < hw - tail0) c += mk[tail0 + t] != 0;
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&area[blockIdx.y], c);
 }
@@ -462,7 +462,7 @@ int launch_frame_kitti(const FrameParamsDev& prm, const float* velo, int64_t n_v
     }
     if (n_masks > 0) {
         const int hw = prm.img_w * prm.img_h;
-        int gx = (hw + FB_THREADS * 16 - 1) / (FB_THREADS * 16);
+        int gx = (hw / 4 + FB_THREADS * 4 - 1) / (FB_THREADS * 4);
         if (gx < 1) gx = 1;
         k_fb_mask_area<<<dim3(gx, n_masks), FB_THREADS, 0, st>>>(masks, hw, s.area); ++nl;
     }
@@ -479,7 +479,7 @@ int launch_frame_mono(const FrameParamsDev& prm, const uint8_t* masks, int n_mas
     Scratch s = carve(scratch, 0, 1, n_masks, prm.max_bg);
     const int hw = prm.img_w * prm.img_h;
     cudaMemsetAsync(s.area, 0, sizeof(int) * (n_masks + 1), st);
-    int gx = (hw + FB_THREADS * 16 - 1) / (FB_THREADS * 16);
+    int gx = (hw / 4 + FB_THREADS * 4 - 1) / (FB_THREADS * 4);
     if (gx < 1) gx = 1;
     k_fb_mask_area<<<dim3(gx, n_masks), FB_THREADS, 0, st>>>(masks, hw, s.area);
     k_fb_mono<<<1, FB_THREADS, 0, st>>>(masks, n_masks, bboxes, s.area, prm, s.bg_px, rays, info);

@@ -9,6 +9,10 @@
   c4  mesh extraction: 256^3 grid SDF, slabs of the slowest axis per rank + NCCL all-gather, then marching cubes
   c5  throughput sweep: 1024 C1-shaped detections partitioned contiguously across the ranks (no collective);
       objects/s includes packing, H2D of the inputs and D2H of the results
+  frame  detection -> optimiser-input builder on a KITTI-sized synthetic frame (120 k LiDAR
+      points, 12 boxes, 13 masks of 1242x375): CUDA builder (device time by CUDA events, inputs resident; and the
+      public `FrameBuilder.build_kitti` call from host arrays), then frame -> Gauss-Newton without leaving HBM,
+      next to the numpy oracle of the same step on the host cores
 All times are device-synchronised wall times of the public API calls (max over ranks)."""
 import json
 import os
@@ -121,6 +125,54 @@ if "c5" in which:
         good = int(t.item())
     emit(config="C5 throughput sweep: 1024 C1-shaped detections split contiguously over the GPUs, H2D/D2H included",
          seconds=dt, objects_per_s=n_total / dt, good=good)
+
+if "frame" in sys.argv[1:] and world == 1:
+    from dspslam.frame import FrameBuilder
+    from dspslam.frame_synth import IMG_H, IMG_W, K, T_CAM_VELO, synth_kitti_frame
+    from oracle import frame_oracle as fo          # CPU baseline leg only
+    scan, boxes, masks, bbs = synth_kitti_frame(3, n_cars=11, n_ground=110000, pts_per_car=1200)
+    opt = Optimizer(dec, synth.kitti_config(), mode="tc", device=local)
+    fbuild = FrameBuilder(opt.engine, K, np.linalg.inv(K).astype(np.float32), T_CAM_VELO, IMG_W, IMG_H)
+    d_scan = torch.from_numpy(scan).cuda()
+    d_masks = torch.from_numpy(masks.view(np.uint8)).cuda()
+    d_bbs = torch.from_numpy(bbs).cuda()
+    dt_res, fb = timed(lambda: fbuild.build_kitti(d_scan, boxes, d_masks, d_bbs), reps=20, warm=3)
+    dt_host, fb = timed(lambda: fbuild.build_kitti(scan, boxes, masks, bbs), reps=10, warm=2)
+    # device time of the kernels alone (CUDA events around the C-ABI call; build_kitti ends with one small D2H)
+    import ctypes as C
+    from dspslam import _native as N
+    from dspslam.frame import box_frames
+    _, bx, _, _ = box_frames(boxes, T_CAM_VELO)
+    base, o = fb.blob.data_ptr(), fb.offs
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+
+    def kernels():
+        N.check(opt.engine.lib.dspslam_frame_build_kitti(
+            opt.engine._h, opt.engine._stream(), C.byref(fbuild.prm), d_scan.data_ptr(), d_scan.shape[0], bx, fb.B,
+            d_masks.data_ptr(), d_masks.shape[0], d_bbs.data_ptr(), base + o["pts_off"], base + o["ray_off"],
+            base + o["n_fg"], base + o["pts"], base + o["rays"], base + o["depth"], base + o["info"]), "frame")
+    for _ in range(3):
+        kernels()
+    torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(50):
+        kernels()
+    ev[1].record()
+    torch.cuda.synchronize()
+    dt_k = ev[0].elapsed_time(ev[1]) / 50 * 1e-3
+    algo_bytes = scan.nbytes + masks.size + 12 * fb.total_pts + 16 * fb.total_rays    # scan once, masks once, outputs
+    dt_gn, outs = timed(lambda: opt.reconstruct_frame(fb), reps=5, warm=2)
+    invK = np.linalg.inv(K).astype(np.float32)
+    t0 = time.perf_counter()
+    for _ in range(3):
+        ref = fo.kitti_frame(scan, boxes, masks, bbs, K, invK, T_CAM_VELO, IMG_W, IMG_H)
+    dt_cpu = (time.perf_counter() - t0) / 3
+    emit(config="frame builder: %d LiDAR points, %d boxes, %d masks %dx%d -> %d surface pts + %d rays"
+         % (scan.shape[0], boxes.shape[0], masks.shape[0], IMG_W, IMG_H, fb.total_pts, fb.total_rays),
+         us_kernels=dt_k * 1e6, us_build_resident=dt_res * 1e6, us_build_from_host=dt_host * 1e6,
+         algorithmic_bytes=int(algo_bytes), kernels_gbps=algo_bytes / dt_k / 1e9,
+         ms_frame_gn=dt_gn * 1e3, good=sum(1 for x in outs if x.is_good), with_rays=int(fb.info[:, 4].sum()),
+         ms_cpu_numpy_oracle=dt_cpu * 1e3, cpu_cores=os.cpu_count())
 
 if world > 1:
     dist.destroy_process_group()
