@@ -158,11 +158,12 @@ def reference_arm(args, rank, world):
     run_cpu_sample(1, 1)
     vals, secs = [], 0.0
     for _ in range(max(1, args.steps)):
-        v, dt, thr = run_cpu_sample(1, 2)
+        v, dt, thr = run_cpu_sample(1, ITERS)
         vals.append(v)
         secs += dt
     v = float(np.median(vals))
-    sample = "1 detection x 2 of %d GN iterations per step (scaled to %d), %d steps" % (ITERS, ITERS, len(vals))
+    sample = ("1 C2 detection x all %d GN iterations per step (%.1f s of CPU work per step), median of %d steps"
+              % (ITERS, secs / len(vals), len(vals)))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "objects/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * OBJ_PER_RANK / v,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -284,7 +285,12 @@ def ours_arm(args, rank, world, local_rank):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "forward-only decoder over in-ball ray samples (GN render term)",
                      "achieved": fwd_tf, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": fwd_tf / pk["tflops"],
-                     "traffic": None, "peak_source": pk["src"],
+                     # DRAM bytes of one forward launch (read + write) from the committed `ncu --set full` capture of
+                     # this command: profiles/r01_ncu_full_bench_k_tc_v4_summary.txt (weights + 16 B per sample in,
+                     # 4 B out; activations never leave the SM)
+                     "traffic": (16739840 + 13568) if args.mode == "tc" else None,
+                     "traffic_source": "profiles/r01_ncu_full_bench_k_tc_v4_summary.txt (dram__bytes_read+write.sum)",
+                     "peak_source": pk["src"],
                      "avg_launch_ms": prof["ms_gn_fwd"] / max(1, prof["n_gn_fwd"]),
                      "rows_per_launch": prof["rows_gn_fwd"] / max(1, prof["n_gn_fwd"]),
                      "share_of_step": prof["ms_gn_fwd"] / max(1e-9, float(np.sum(step_ms))),
@@ -305,10 +311,10 @@ def ours_arm(args, rank, world, local_rank):
     }
     if world == 1 and not args.no_cpu:
         run_cpu_sample(1, 1)
-        v, dt, thr = run_cpu_sample(1, 3)
+        v, dt, thr = run_cpu_sample(1, ITERS)
         line["cpu_baseline"] = {"value": v, "unit": "objects/s", "cores": thr, "kind": "port",
-                                "sample": "1 detection x 3 of %d GN iterations, scaled to %d (%.1f s of CPU work)"
-                                          % (ITERS, ITERS, dt)}
+                                "sample": "1 of the %d C2 detections x all %d GN iterations (%.1f s of CPU work)"
+                                          % (OBJ_PER_RANK, ITERS, dt)}
     else:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)

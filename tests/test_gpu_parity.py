@@ -388,3 +388,38 @@ def test_flip_hypotheses_batched_vs_oracle(wfit, odec):
     assert abs(one.loss - kept[1].loss) < 1e-5
     # the wrong half turn must lose: the kept hypothesis of detection 1 is the flipped twin
     assert both[1][1].loss < both[1][0].loss and kept[1].loss == both[1][1].loss
+
+
+def test_two_host_threads_share_one_optimizer(wfit):
+    """The boundary's threading model: the tracking and local-mapping threads of the C++ system call
+    the same Optimizer; ctypes releases the GIL during the native call, so calls do overlap here.  Results must
+    equal the serial ones bit for bit (per-handle mutex, per-call workspace carve-up)."""
+    import threading
+    from dspslam import synth
+    from reconstruct.optimizer import Optimizer
+    cfg = synth.kitti_config()
+    cfg.optimizer.joint_optim.num_iterations = 3
+    opt = Optimizer(wfit, cfg, mode="tc")
+    dets = [synth.make_kitti_detection(k, M=150 + 30 * k, n_bg=50 + 10 * k) for k in range(6)]
+    serial = [opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"]) for d in dets]
+    got = [None] * len(dets)
+    errs = []
+
+    def work(lo, hi):
+        try:
+            for _ in range(3):
+                for k in range(lo, hi):
+                    d = dets[k]
+                    got[k] = opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
+        except Exception as e:                                    # pragma: no cover
+            errs.append(e)
+
+    th = [threading.Thread(target=work, args=(0, 3)), threading.Thread(target=work, args=(3, 6))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not errs
+    for a, b in zip(serial, got):
+        assert a.is_good == b.is_good and a.loss == b.loss
+        assert np.array_equal(a.t_cam_obj, b.t_cam_obj) and np.array_equal(a.code, b.code)
