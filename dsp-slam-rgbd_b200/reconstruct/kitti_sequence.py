@@ -19,18 +19,19 @@ from reconstruct.utils import ForceKeyErrorDict  # noqa: F401  (instances are Fo
 
 
 def read_calib_file(filepath):
-    """KITTI calibration file -> dict of float arrays (`reconstruct/utils.py:60-74`)."""
-    data = {}
-    with open(filepath) as f:
-        for line in f:
-            if line == "\n":
+    """KITTI `calib.txt` -> {key: float64 array}; parsing stops at the first blank line and entries that are not
+    numeric (dates) are dropped, as in `reconstruct/utils.py:60-74`."""
+    out = {}
+    with open(filepath) as fh:
+        for raw in fh:
+            if raw == "\n":
                 break
-            key, value = line.split(":", 1)
+            name, _, rest = raw.partition(":")
             try:
-                data[key] = np.array([float(x) for x in value.split()])
+                out[name] = np.array(rest.split(), dtype=np.float64)
             except ValueError:
-                pass
-    return data
+                continue
+    return out
 
 
 def load_velo_scan(file):
@@ -96,14 +97,16 @@ class KITIISequence:
         self.detections_in_current_frame = None
 
     def load_calib(self):
-        filedata = read_calib_file(self.calib_file)
-        P_cam2_cam0 = np.reshape(filedata["P2"], (3, 4))
-        self.K_cam = P_cam2_cam0[0:3, 0:3].astype(np.float32)
+        """Intrinsics of camera 2 and the velodyne -> camera-2 transform, FP32 (`kitti_sequence.py:243-257`):
+        K = P2[:, :3]; camera 2 sits P2[0,3]/P2[0,0] along x from camera 0, whose pose in the velodyne frame is Tr."""
+        cal = read_calib_file(self.calib_file)
+        P2 = cal["P2"].reshape(3, 4)
+        self.K_cam = P2[:, :3].astype(np.float32)
         self.invK_cam = np.linalg.inv(self.K_cam).astype(np.float32)
-        T_cam0_velo, T_cam2_cam0 = np.eye(4), np.eye(4)
-        T_cam0_velo[:3, :] = np.reshape(filedata["Tr"], (3, 4))
-        T_cam2_cam0[0, 3] = P_cam2_cam0[0, 3] / P_cam2_cam0[0, 0]
-        self.T_cam_velo = T_cam2_cam0.dot(T_cam0_velo).astype(np.float32)
+        cam0_from_velo = np.vstack([cal["Tr"].reshape(3, 4), [0.0, 0.0, 0.0, 1.0]])
+        cam2_from_cam0 = np.eye(4)
+        cam2_from_cam0[0, 3] = P2[0, 3] / P2[0, 0]
+        self.T_cam_velo = cam2_from_cam0.dot(cam0_from_velo).astype(np.float32)
 
     def get_frame_by_id(self, frame_id, **arrays):
         self.current_frame = FrameWithLiDAR(self, frame_id, **arrays)

@@ -208,3 +208,66 @@ def test_gpu_frame_to_gauss_newton_on_device(eng):
     fr = FrameWithLiDAR(seq, 0, velo_pts=scan, detections_3d=boxes, det_2d={"pred_masks": masks, "pred_boxes": bbs})
     fr.get_detections()
     check_instances(fr.instances, g, lambda ins, k: ins[k])
+
+
+# ---- CPU: host-side logic of the builder and the boundary structs --------------------------------------------------
+def test_box_frames_host_bookkeeping_matches_oracle():
+    from dspslam.frame import box_frames
+    from dspslam.frame_synth import T_CAM_VELO, synth_kitti_frame
+    from oracle import frame_oracle as fo
+    _, boxes, _, _ = synth_kitti_frame(4, n_cars=6, n_ground=100)
+    order, cb, T_co, sizes = box_frames(boxes, T_CAM_VELO)
+    oorder, ob = fo.box_frames(boxes, T_CAM_VELO)
+    assert np.array_equal(order, oorder)
+    for i, o in enumerate(ob):
+        assert np.array_equal(np.array(cb[i].T_obj_velo[:], np.float32).reshape(3, 4), o["T_obj_velo"][:3])
+        assert np.array_equal(np.array(cb[i].lo[:], np.float32), o["lo"])
+        assert np.array_equal(np.array(cb[i].hi[:], np.float32), o["hi"])
+        assert np.array_equal(np.array(cb[i].half[:], np.float32), o["half"])
+        assert np.array_equal(T_co[i], o["T_cam_obj"]) and np.array_equal(sizes[i], o["scale"])
+        assert bool(cb[i].is_front) == bool(o["T_cam_obj"][2, 3] > 0)
+
+
+def test_frame_structs_match_the_c_header(tmp_path):
+    """ctypes mirrors of dspslam_frame_params / dspslam_frame_box have the size and field offsets gcc gives the
+    declarations in include/dspslam.h."""
+    import ctypes
+    import subprocess
+    from dspslam import _native as N
+    src = tmp_path / "s.c"
+    src.write_text('#include <stdio.h>\n#include <stddef.h>\n#include "dspslam.h"\nint main(void){'
+                   'printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(dspslam_frame_params), offsetof(dspslam_frame_params, K),'
+                   'offsetof(dspslam_frame_params, T_cam_velo), offsetof(dspslam_frame_params, k1),'
+                   'offsetof(dspslam_frame_params, invK64), sizeof(dspslam_frame_box), offsetof(dspslam_frame_box, is_front));'
+                   'printf("%zu %zu\\n", sizeof(dspslam_joint_params), sizeof(dspslam_profile));return 0;}')
+    exe = tmp_path / "s"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    a, b = subprocess.check_output([str(exe)]).decode().split("\n")[:2]
+    got = [int(v) for v in a.split()]
+    P, B = N.FrameParams, N.FrameBox
+    assert got == [ctypes.sizeof(P), P.K.offset, P.T_cam_velo.offset, P.k1.offset, P.invK64.offset,
+                   ctypes.sizeof(B), B.is_front.offset]
+    assert [int(v) for v in b.split()] == [ctypes.sizeof(N.JointParams), ctypes.sizeof(N.Profile)]
+
+
+def test_kitti_sequence_calibration(tmp_path):
+    """KITIISequence.load_calib (kitti_sequence.py:243-257): K = P2[:, :3], T_cam_velo = [I | (P2[0,3]/fx, 0, 0)] Tr."""
+    import types
+    from reconstruct.kitti_sequence import KITIISequence
+    (tmp_path / "calib.txt").write_text(
+        "P0: 7.18856e+02 0 6.071928e+02 0 0 7.18856e+02 1.852157e+02 0 0 0 1 0\n"
+        "P2: 7.18856e+02 0 6.071928e+02 4.538225e+01 0 7.18856e+02 1.852157e+02 -1.130887e-01 0 0 1 3.779761e-03\n"
+        "Tr: 4.276802e-04 -9.999672e-01 -8.084491e-03 -1.198459e-02 -7.210626e-03 8.081198e-03 -9.999413e-01 "
+        "-5.403984e-02 9.999738e-01 4.859485e-04 -7.206933e-03 -2.921968e-01\n")
+    seq = KITIISequence.__new__(KITIISequence)
+    seq.calib_file = str(tmp_path / "calib.txt")
+    seq.load_calib()
+    assert seq.K_cam.dtype == np.float32 and seq.T_cam_velo.dtype == np.float32
+    assert np.allclose(seq.K_cam, [[718.856, 0, 607.1928], [0, 718.856, 185.2157], [0, 0, 1]])
+    assert np.allclose(seq.K_cam.astype(np.float64) @ seq.invK_cam.astype(np.float64), np.eye(3), atol=1e-4)
+    Tr = np.array([4.276802e-04, -9.999672e-01, -8.084491e-03, -1.198459e-02, -7.210626e-03, 8.081198e-03, -9.999413e-01,
+                   -5.403984e-02, 9.999738e-01, 4.859485e-04, -7.206933e-03, -2.921968e-01]).reshape(3, 4)
+    want = np.vstack([Tr, [0, 0, 0, 1]])
+    want[0, 3] += 4.538225e+01 / 7.18856e+02
+    assert np.allclose(seq.T_cam_velo, want, atol=1e-6)
+    _ = types
