@@ -278,6 +278,23 @@ class Engine:
         dbg = self.run_joint(batch, params, mode=mode, debug=debug)
         return self.download_joint(batch, dbg)
 
+    def gn_pose_only_resident(self, batch, t_co_se3, scales, codes, num_iterations, mode=None):
+        """Pose-only GN on the surface points of a resident batch (JointBatch / FrameBatch: `pts_off`, `pts` already in
+        HBM): only the (B,4,4) SE(3) poses, B scales and B codes go up, (B,4,4) comes back."""
+        t = self.torch
+        B, L = batch.B, self.code_len
+        T = np.ascontiguousarray(np.asarray(t_co_se3, np.float32).reshape(B, 16))
+        sc = np.ascontiguousarray(np.asarray(scales, np.float32).reshape(B))
+        Cd = np.ascontiguousarray(np.asarray(codes, np.float32).reshape(B, -1)[:, :L])
+        if Cd.shape[1] < L:
+            Cd = np.concatenate([Cd, np.zeros((B, L - Cd.shape[1]), np.float32)], 1)
+        d_T, d_sc, d_code = (t.from_numpy(a).to(self.device) for a in (T, sc, Cd))
+        N.check(self.lib.dspslam_gn_pose_only(
+            self._h, self._stream(), self._mode(mode), num_iterations, B, batch.ptr("pts_off"), batch.ptr("pts"),
+            batch.total_pts, batch.max_pts, d_sc.data_ptr(), d_code.data_ptr(), d_T.data_ptr(), None),
+            "dspslam_gn_pose_only")
+        return d_T.cpu().numpy().reshape(B, 4, 4)
+
     def gn_pose_only(self, items, num_iterations, mode=None, debug=False):
         """items: iterable of (t_co_se3 (4,4), scale, pts (M,3), code).  Returns (B,4,4) float32 [, dbg]."""
         t = self.torch

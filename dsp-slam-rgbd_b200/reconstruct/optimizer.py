@@ -147,6 +147,17 @@ class Optimizer(object):
                 outs.append(ForceKeyErrorDict(t_cam_obj=None, code=None, is_good=False, loss=float(res.loss[b])))
         return (outs, res) if debug else outs
 
+    def estimate_poses_frame(self, frame_batch, t_co_se3, scales, codes):
+        """`estimate_pose_cam_obj` for every detection of a device-resident frame (the re-observation loop of
+        `src/LocalMapping_util.cc:94-111`: SE(3) pose from the detector, scale and code of the associated map
+        object), on the surface points the frame builder left in HBM.  Arguments are per detection in the frame's
+        depth order; returns (B, 4, 4) float32."""
+        fb = frame_batch
+        if fb.total_pts == 0:
+            return np.asarray(t_co_se3, np.float32).reshape(fb.B, 4, 4).copy()
+        return self.engine.gn_pose_only_resident(fb, t_co_se3, scales, codes, self.num_iterations_pose_only,
+                                                 mode=self.mode)
+
     # ---- orientation disambiguation, src/LocalMapping_util.cc:398-410 ---------------------------
     @staticmethod
     def flipped(t_cam_obj):

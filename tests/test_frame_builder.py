@@ -271,3 +271,30 @@ def test_kitti_sequence_calibration(tmp_path):
     want[0, 3] += 4.538225e+01 / 7.18856e+02
     assert np.allclose(seq.T_cam_velo, want, atol=1e-6)
     _ = types
+
+
+@pytest.mark.gpu
+def test_gpu_frame_pose_only_on_resident_points(eng):
+    """Re-observation path (src/LocalMapping_util.cc:94-111): pose-only GN on the surface points the builder left in
+    HBM equals the host-array path `estimate_poses_cam_obj` on copies of the same points."""
+    from dspslam import synth
+    from reconstruct.optimizer import Optimizer
+    g, (scan, boxes, masks, bbs) = frame(0)
+    opt = Optimizer(synth.load_wfit(), synth.kitti_config(), mode="fp32")
+    b = _builder(opt.engine)
+    fb = b.build_kitti(scan, boxes, masks, bbs)
+    inst = b.instances(fb)
+    T, sc = [], []
+    for i in inst:
+        s = float(np.cbrt(np.linalg.det(i.T_cam_obj[:3, :3].astype(np.float64))))
+        se3 = i.T_cam_obj.copy()
+        se3[:3, :3] /= np.float32(s)
+        T.append(se3)
+        sc.append(s)
+    codes = np.zeros((fb.B, 64), np.float32)
+    codes[:, :3] = 0.1
+    got = opt.estimate_poses_frame(fb, np.stack(T), sc, codes)
+    want = opt.estimate_poses_cam_obj([(T[k], sc[k], inst[k].surface_points, codes[k]) for k in range(fb.B)])
+    assert got.shape == (fb.B, 4, 4) and np.isfinite(got).all()
+    assert np.allclose(got, want, atol=1e-6)
+    assert np.abs(got - np.stack(T)).max() > 1e-4            # the optimisation moved the poses
