@@ -623,11 +623,10 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_jac_simt(GnWork w) {
 // iteration.  optimizer.py:157-194 (joint) / :69-75 (pose only).  One CTA per object.
 //
 // The reference solves with torch.inverse(H) b in FP32.  Here H (symmetric positive definite after damping)
-// is factorised in FP64 as L D L^T, left-looking, one barrier per column: thread i owns row i; column j is
-//   w_ij = H_ij - sum_{k<j} u_ik w_jk,   D_j = w_jj,   u_ij = w_ij / D_j  (= L_ij)
-// with w kept in the lower triangle and u in the (otherwise redundant) upper triangle, transposed, so that a
-// thread's own-row reads are conflict-free and the pivot row is a broadcast.  b rides along as row `dim`
-// (its u lives in xs), which makes the forward substitution part of the same loop.
+// is factorised in FP64 as L D L^T, right-looking (rank-1 updates of the trailing lower triangle):
+//   D_j = w_jj,   u_ij = w_ij / D_j  (= L_ij),   w_ik -= u_ij w_kj   (j < k <= i)
+// with w kept in the lower triangle and u in the (otherwise redundant) upper triangle, transposed.  b rides
+// along as row `dim` (its u lives in xs), which makes the forward substitution part of the same loop.
 // ---------------------------------------------------------------------------
 constexpr int SOLVE_NT = 512;
 
@@ -724,40 +723,26 @@ __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int l
             }
             __syncthreads();
         }
-        // L D L^T, left-looking; thread i = row i (row dim = b)
+        // L D L^T, right-looking: per column j   l_i = w_ij / D_j  (threads i = j+1 .. dim),  then the rank-1 update
+        // w_ik -= l_i w_kj of the trailing lower triangle by all threads (warp = row group, lane = column: the l_i are
+        // broadcasts, the rows are read contiguously).  Two short barriers per column instead of one barrier behind a
+        // j-long dot product: the dependent chain per column is one reciprocal and one multiply-add.
         {
-            const int i = tid;
+            const int ty = tid >> 5, tx = tid & 31;
             for (int j = 0; j < dim; ++j) {
-                double acc = 0.0;
-                if (i >= j && i <= dim) {
-                    double a0 = Hs[i * n + j], a1 = 0.0;
-                    const double* wj = Hs + j * n;
-                    if (i < dim) {
-                        int k = 0;
-                        for (; k + 2 <= j; k += 2) {
-                            a0 = fma(-Hs[k * n + i], wj[k], a0);
-                            a1 = fma(-Hs[(k + 1) * n + i], wj[k + 1], a1);
-                        }
-                        if (k < j) a0 = fma(-Hs[k * n + i], wj[k], a0);
-                    } else {
-                        int k = 0;
-                        for (; k + 2 <= j; k += 2) {
-                            a0 = fma(-xs[k], wj[k], a0);
-                            a1 = fma(-xs[k + 1], wj[k + 1], a1);
-                        }
-                        if (k < j) a0 = fma(-xs[k], wj[k], a0);
-                    }
-                    acc = a0 + a1;
-                    Hs[i * n + j] = acc;
+                if (tid > j && tid <= dim) {
+                    const double u = Hs[tid * n + j] / Hs[j * n + j];
+                    if (tid < dim) Hs[j * n + tid] = u; else xs[j] = u;
                 }
                 __syncthreads();
-                if (i > j && i <= dim) {
-                    const double u = acc / Hs[j * n + j];
-                    if (i < dim) Hs[j * n + i] = u; else xs[j] = u;
+                for (int i = j + 1 + ty; i <= dim; i += SOLVE_NT / 32) {
+                    const double li = (i < dim) ? Hs[j * n + i] : xs[j];
+                    double* hi = Hs + i * n;
+                    for (int k = j + 1 + tx; k <= i && k < dim; k += 32) hi[k] = fma(-li, Hs[k * n + j], hi[k]);
                 }
+                __syncthreads();
             }
         }
-        __syncthreads();
         // back substitution L^T x = y (y = xs), column-oriented, warp 0: lane holds x[lane], x[lane+32], x[lane+64]
         if (tid < 32) {
             double x0 = (tid < dim) ? xs[tid] : 0.0, x1 = (tid + 32 < dim) ? xs[tid + 32] : 0.0,
