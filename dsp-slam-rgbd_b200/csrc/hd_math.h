@@ -195,10 +195,16 @@ DSP_HD float ray_depth(const RayParams& p, int j) {
     return p.dtab ? p.dtab[j] : linspace_at(p.dmin, p.dmax, p.D, j);
 }
 
+// `acc` is scratch for D floats addressed as acc[j * acc_stride] (the CUDA kernel hands in a shared-memory column:
+// a dynamically indexed local array would live in local memory).
 template <class Emit>
-DSP_HD int ray_scan(const float* sdf, int stride, float depth_obs, const RayParams& p, Emit emit) {
+DSP_HD int ray_scan_scratch(const float* sdf, int stride, float depth_obs, const RayParams& p, float* acc_base,
+                            int acc_stride, Emit emit) {
     const int D = p.D;
-    float acc[DSP_MAX_D];
+    struct Acc {
+        float* b; int s;
+        DSP_HD float& operator[](int j) const { return b[j * s]; }
+    } acc{acc_base, acc_stride};
     // pass 1: transmittance acc_j = prod_{i<=j} (1-o_i) and expected depth
     //         d_u = sum_j d_j * o_j * acc_{j-1} + 1.1*dmax * acc_{D-1}
     // Once the transmittance is exactly 0 every later term is exactly 0: stop there (jend).
@@ -236,6 +242,12 @@ DSP_HD int ray_scan(const float* sdf, int stride, float depth_obs, const RayPara
         }
     }
     return n;
+}
+
+template <class Emit>
+DSP_HD int ray_scan(const float* sdf, int stride, float depth_obs, const RayParams& p, Emit emit) {
+    float acc[DSP_MAX_D];
+    return ray_scan_scratch(sdf, stride, depth_obs, p, acc, 1, emit);
 }
 
 }  // namespace dsp

@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_fwd_simt(GnWork w) {
 constexpr int RAY_NT = 128;
 
 __global__ void __launch_bounds__(RAY_NT) k_gn_ray_count(GnWork w) {
-    extern __shared__ float s_sdf[];                           // [RAY_NT][D + 1]
+    extern __shared__ float s_sdf[];                           // [RAY_NT][D + 1] samples, then [D][RAY_NT] scan scratch
     __shared__ int s_part[RAY_NT];
     __shared__ int s_last_obj;
     const int b = blockIdx.y, tid = threadIdx.x;
@@ -403,7 +403,8 @@ __global__ void __launch_bounds__(RAY_NT) k_gn_ray_count(GnWork w) {
     if (live && i0 < N) {
         const int nr = min(RAY_NT, N - i0);
         const float* src = w.sdf_samp + (size_t)(r0 + i0) * D;
-        for (int e = tid; e < nr * D; e += RAY_NT) s_sdf[(e / D) * pitch + (e % D)] = src[e];
+        for (int row = tid >> 5; row < nr; row += RAY_NT / 32)          // warp per ray row: no div/mod, coalesced
+            for (int c = tid & 31; c < D; c += 32) s_sdf[row * pitch + c] = src[(size_t)row * D + c];
         __syncthreads();
         if (tid < nr) {
             const int i = i0 + tid, r = r0 + i;
@@ -417,7 +418,8 @@ __global__ void __launch_bounds__(RAY_NT) k_gn_ray_count(GnWork w) {
             const float rx = w.rays[(size_t)r * 3 + 0], ry = w.rays[(size_t)r * 3 + 1], rz = w.rays[(size_t)r * 3 + 2];
             float4* stage = w.frows + (size_t)r * D;
             float res_ray = 0.f;
-            const int cnt = ray_scan(sdf, 1, dobs, p, [&](int k, float de_ds, float res) {
+            float* acc = s_sdf + RAY_NT * pitch + tid;            // column tid of the [D][RAY_NT] scratch: conflict-free
+            const int cnt = ray_scan_scratch(sdf, 1, dobs, p, acc, RAY_NT, [&](int k, float de_ds, float res) {
                 float x, y, z;
                 sample_point(s.T_oc, rx, ry, rz, p.dtab[k], x, y, z);
                 *stage++ = make_float4(x, y, z, de_ds);
@@ -796,6 +798,9 @@ cudaError_t simt_configure() {
     if ((e = cudaFuncSetAttribute(k_sdf_jac_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
     if ((e = cudaFuncSetAttribute(k_gn_fwd_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
     if ((e = cudaFuncSetAttribute(k_gn_jac_simt, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes))) return e;
+    if ((e = cudaFuncSetAttribute(k_gn_ray_count, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)(sizeof(float) * RAY_NT * (2 * 64 + 1)))))
+        return e;
     return cudaSuccess;
 }
 
@@ -844,7 +849,7 @@ void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st) {
 }
 void launch_gn_rays(const GnWork& w, int max_rays, cudaStream_t st) {
     const int chunks = w.ray_chunks;
-    k_gn_ray_count<<<dim3(chunks, w.B), RAY_NT, sizeof(float) * RAY_NT * (w.prm.D + 1), st>>>(w);
+    k_gn_ray_count<<<dim3(chunks, w.B), RAY_NT, sizeof(float) * RAY_NT * (2 * w.prm.D + 1), st>>>(w);
     k_gn_ray_emit<<<(w.total_rays + 255) / 256 > 0 ? (w.total_rays + 255) / 256 : 1, 256, 0, st>>>(w);
 }
 void launch_gn_jac_simt(const GnWork& w, cudaStream_t st) {
