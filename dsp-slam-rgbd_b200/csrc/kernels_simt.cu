@@ -403,8 +403,16 @@ __global__ void __launch_bounds__(RAY_NT) k_gn_ray_count(GnWork w) {
     if (live && i0 < N) {
         const int nr = min(RAY_NT, N - i0);
         const float* src = w.sdf_samp + (size_t)(r0 + i0) * D;
-        for (int row = tid >> 5; row < nr; row += RAY_NT / 32)          // warp per ray row: no div/mod, coalesced
-            for (int c = tid & 31; c < D; c += 32) s_sdf[row * pitch + c] = src[(size_t)row * D + c];
+        {   // flat coalesced copy, (row, column) advanced incrementally (no div/mod), eight loads in flight
+            const int n_el = nr * D, drow = RAY_NT / D, dcol = RAY_NT % D;
+            int row = tid / D, col = tid % D;
+#pragma unroll 8
+            for (int e = tid; e < n_el; e += RAY_NT) {
+                s_sdf[row * pitch + col] = __ldg(src + e);
+                row += drow; col += dcol;
+                if (col >= D) { col -= D; ++row; }
+            }
+        }
         __syncthreads();
         if (tid < nr) {
             const int i = i0 + tid, r = r0 + i;
