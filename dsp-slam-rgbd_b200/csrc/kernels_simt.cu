@@ -733,22 +733,41 @@ __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int l
             }
             __syncthreads();
         }
-        // L D L^T, right-looking: per column j   l_i = w_ij / D_j  (threads i = j+1 .. dim),  then the rank-1 update
-        // w_ik -= l_i w_kj of the trailing lower triangle by all threads (warp = row group, lane = column: the l_i are
-        // broadcasts, the rows are read contiguously).  Two short barriers per column instead of one barrier behind a
-        // j-long dot product: the dependent chain per column is one reciprocal and one multiply-add.
+        // L D L^T, right-looking and blocked in panels of LDL_P columns.  Panel: thread i = row i (rows j0..dim live
+        // in warps 0-2), per column  l_i = w_ic / D_c, then the thread updates the rest of ITS row inside the panel;
+        // one 96-thread named barrier per column.  Trailing matrix: all threads (warp = row group, lane = column),
+        // one rank-LDL_P update  w_ik -= sum_c l_ic w_kc  between two CTA barriers per panel.
         {
+            constexpr int LDL_P = 4;
             const int ty = tid >> 5, tx = tid & 31;
-            for (int j = 0; j < dim; ++j) {
-                if (tid > j && tid <= dim) {
-                    const double u = Hs[tid * n + j] / Hs[j * n + j];
-                    if (tid < dim) Hs[j * n + tid] = u; else xs[j] = u;
+            for (int j0 = 0; j0 < dim; j0 += LDL_P) {
+                const int j1 = min(j0 + LDL_P, dim);
+                if (tid < 96) {
+                    for (int c = j0; c < j1; ++c) {
+                        if (tid > c && tid <= dim) {
+                            const double u = Hs[tid * n + c] / Hs[c * n + c];
+                            if (tid < dim) Hs[c * n + tid] = u; else xs[c] = u;
+                            for (int c2 = c + 1; c2 < j1 && c2 <= tid; ++c2)
+                                Hs[tid * n + c2] = fma(-u, Hs[c2 * n + c], Hs[tid * n + c2]);
+                        }
+                        asm volatile("bar.sync 2, 96;" ::: "memory");
+                    }
                 }
                 __syncthreads();
-                for (int i = j + 1 + ty; i <= dim; i += SOLVE_NT / 32) {
-                    const double li = (i < dim) ? Hs[j * n + i] : xs[j];
+                for (int i = j1 + ty; i <= dim; i += SOLVE_NT / 32) {
+                    double li[LDL_P];
+#pragma unroll
+                    for (int c = 0; c < LDL_P; ++c)
+                        li[c] = (j0 + c < j1) ? ((i < dim) ? Hs[(j0 + c) * n + i] : xs[j0 + c]) : 0.0;
                     double* hi = Hs + i * n;
-                    for (int k = j + 1 + tx; k <= i && k < dim; k += 32) hi[k] = fma(-li, Hs[k * n + j], hi[k]);
+                    for (int k = j1 + tx; k <= i && k < dim; k += 32) {
+                        const double* wk = Hs + k * n + j0;
+                        double acc = hi[k];
+#pragma unroll
+                        for (int c = 0; c < LDL_P; ++c)
+                            if (j0 + c < j1) acc = fma(-li[c], wk[c], acc);
+                        hi[k] = acc;
+                    }
                 }
                 __syncthreads();
             }
