@@ -28,3 +28,13 @@ def pytest_collection_modifyitems(config, items):
 @pytest.fixture(scope="session")
 def golden_dir():
     return GOLDEN
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _native_library_built():
+    """A fresh checkout has no built library (built artefacts are git-ignored): build it once per session
+    (`__graft_entry__.build()`: nvcc for sm_100a, works without a GPU)."""
+    from dspslam import _native
+    if not os.path.isfile(_native.LIB_PATH) or not os.path.isfile(os.path.join(PKG, "csrc", "libhd_selftest.so")):
+        import __graft_entry__ as g
+        g.build()
