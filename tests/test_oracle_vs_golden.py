@@ -159,6 +159,13 @@ def test_c3_mono(k, dec_fit):
 
 
 @pytest.mark.parametrize("k", [0, 1])
+def test_c3_freiburg(k, dec_fit):
+    """configs/config_freiburg_001.json (k1 = 1, k3 = 0.5, scale damping 100), the reference's own 50 samples."""
+    g = load("c3f_obj%d.npz" % k)
+    _teacher_forced(g, dec_fit, lambda: synth.freiburg_config(iters=10, num_depth_samples=50), [0, 1, 4, 9])
+
+
+@pytest.mark.parametrize("k", [0, 1])
 def test_pose_only(k, dec_fit):
     g = load("pose_only_obj%d.npz" % k)
     opt = orc.OracleOptimizer(dec_fit, synth.kitti_config())
