@@ -13,6 +13,11 @@
       points, 12 boxes, 13 masks of 1242x375): CUDA builder (device time by CUDA events, inputs resident; and the
       public `FrameBuilder.build_kitti` call from host arrays), then frame -> Gauss-Newton without leaving HBM,
       next to the numpy oracle of the same step on the host cores
+  torchq  like-for-like GPU data point for the per-query metrics: the decoder queried with STOCK PyTorch FP32 on the
+      same B200 the way the reference issues its queries (one shared code expanded and concatenated to (n, 67) rows,
+      chunks of 64^3, `no_grad` forward for decode_sdf - loss_utils.py:51-79; forward + one reverse-mode pass with a
+      ones cotangent for get_batch_sdf_jacobian - loss_utils.py:82-113; weight-norm hooks active, TF32 off), next to
+      this library's kernels on the same rows.  A port of the query pattern, not the reference's files.
 All times are device-synchronised wall times of the public API calls (max over ranks)."""
 import json
 import os
@@ -173,6 +178,55 @@ if "frame" in sys.argv[1:] and world == 1:
          algorithmic_bytes=int(algo_bytes), kernels_gbps=algo_bytes / dt_k / 1e9,
          ms_frame_gn=dt_gn * 1e3, good=sum(1 for x in outs if x.is_good), with_rays=int(fb.info[:, 4].sum()),
          ms_cpu_numpy_oracle=dt_cpu * 1e3, cpu_cores=os.cpu_count())
+
+if "torchq" in sys.argv[1:] and world == 1:
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    net = synth.load_wfit().cuda().eval()
+    eng = Optimizer(dec, synth.kitti_config(), mode="tc", device=local).engine
+    code = torch.zeros(64, device="cuda")
+    code[:3] = torch.tensor([0.2, -0.1, 0.3])
+    n_f, n_j = 128 ** 3, 75776                       # the sizes of tools/prof_kernels.py
+    xf = torch.rand((n_f, 3), device="cuda") * 1.6 - 0.8
+    xj = torch.rand((n_j, 3), device="cuda") * 1.6 - 0.8
+
+    def torch_forward():
+        outs = []
+        with torch.no_grad():
+            for head in range(0, n_f, 64 ** 3):
+                x = xf[head: head + 64 ** 3]
+                outs.append(net(torch.cat([code.expand(x.shape[0], -1), x], dim=1)).squeeze(1))
+        return torch.cat(outs)
+
+    def torch_jacobian():
+        inp = torch.cat([code.expand(n_j, -1), xj], dim=1).unsqueeze(1).requires_grad_(True)
+        y = net(inp)
+        y.backward(torch.ones_like(y))                # out_dim = 1: the identity cotangent is a vector of ones
+        return y.detach(), inp.grad
+
+    def ev_time(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            out = fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps * 1e-3, out
+
+    t_tf, s_t = ev_time(torch_forward, 3)
+    t_tj, (y_t, j_t) = ev_time(torch_jacobian, 5)
+    cnp = code.cpu().numpy()
+    t_of, s_o = ev_time(lambda: eng.sdf(cnp, xf), 5)
+    t_oj, (y_o, j_o) = ev_time(lambda: eng.sdf_jac(cnp, xj), 5)
+    emit(config="per-query throughput on one B200: stock PyTorch FP32 (cuBLAS SGEMM + autograd) vs this library (tcgen05)",
+         torch_forward_mquery_s=n_f / t_tf / 1e6, torch_jacobian_mquery_s=n_j / t_tj / 1e6,
+         ours_forward_mquery_s=n_f / t_of / 1e6, ours_jacobian_mquery_s=n_j / t_oj / 1e6,
+         forward_speedup=t_tf / t_of, jacobian_speedup=t_tj / t_oj,
+         max_abs_sdf_diff=float((s_t - s_o).abs().max()),
+         jac_rms_diff=float(((j_t.squeeze(1) - j_o) ** 2).mean().sqrt()))
 
 if world > 1:
     dist.destroy_process_group()
