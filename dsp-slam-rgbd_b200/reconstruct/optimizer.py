@@ -85,7 +85,19 @@ class Optimizer(object):
         return self.estimate_poses_cam_obj([(t_co_se3, scale, pts, code)])[0]
 
     def estimate_poses_cam_obj(self, items, debug=False):
-        return self.engine.gn_pose_only(items, self.num_iterations_pose_only, mode=self.mode, debug=debug)
+        items = list(items)
+        if not items:
+            return np.zeros((0, 4, 4), np.float32)
+        # no surface points: the reference's normal equations are 0/0 and it returns a NaN pose (optimizer.py:70-75);
+        # same answer here, without a launch (and without an exception across the pybind11 boundary)
+        live = [k for k, it in enumerate(items) if np.asarray(it[2]).reshape(-1, 3).shape[0] > 0]
+        if len(live) == len(items):
+            return self.engine.gn_pose_only(items, self.num_iterations_pose_only, mode=self.mode, debug=debug)
+        out = np.full((len(items), 4, 4), np.nan, np.float32)
+        if live:
+            res = self.engine.gn_pose_only([items[k] for k in live], self.num_iterations_pose_only, mode=self.mode)
+            out[live] = res
+        return (out, None) if debug else out
 
     # ---- joint pose + shape, optimizer.py:90-205 ------------------------------------------------
     def reconstruct_object(self, t_cam_obj, pts, rays, depth, code=None):
@@ -115,6 +127,8 @@ class Optimizer(object):
                 if code.shape[0] < self.engine.code_len:
                     code = np.concatenate([code, np.zeros(self.engine.code_len - code.shape[0], np.float32)])
             dets.append((d[0], d[1], d[2], d[3], code))
+        if not dets:
+            return ([], None) if debug else []
         res = self.engine.gn_joint(dets, self._params(), mode=self.mode, debug=debug)
         outs = []
         for b in range(len(dets)):
@@ -194,6 +208,8 @@ class Optimizer(object):
     # ---- optimizer.py:207-213 ---------------------------------------------------------------------
     def compute_sdf_loss_objectpoint_zhjd(self, pts_surface_obj, code):
         code = np.asarray(code, np.float32)[: self.code_len]
+        if np.asarray(pts_surface_obj).reshape(-1, 3).shape[0] == 0:
+            return float("nan")                                   # mean over zero rows, as torch gives
         mean_value = float(self.engine.mean_sdf(code, np.asarray(pts_surface_obj, np.float32), mode=self.mode).item())
         if self.verbose:
             print("[mapobject sdf loss]python:", mean_value)

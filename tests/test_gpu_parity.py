@@ -434,3 +434,32 @@ def test_two_host_threads_share_one_optimizer(wfit):
     for a, b in zip(serial, got):
         assert a.is_good == b.is_good and a.loss == b.loss
         assert np.array_equal(a.t_cam_obj, b.t_cam_obj) and np.array_equal(a.code, b.code)
+
+
+def test_degenerate_inputs_do_not_raise(wfit):
+    """No exception may cross the pybind11 boundary: empty batches, missing points, NaN inputs and other
+    dtypes / memory orders give the reference's answers (is_good False / NaN) instead of raising."""
+    from dspslam import synth
+    from reconstruct.optimizer import Optimizer
+    cfg = synth.kitti_config()
+    cfg.optimizer.joint_optim.num_iterations = 2
+    opt = Optimizer(wfit, cfg, mode="tc")
+    d = synth.make_kitti_detection(0)
+    base = opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
+    assert base.is_good
+    f64 = opt.reconstruct_object(d["t_cam_obj"].astype(np.float64), np.asfortranarray(d["pts"].astype(np.float64)),
+                                 d["rays"].astype(np.float64), d["depth"].astype(np.float64))
+    assert f64.is_good and np.array_equal(f64.t_cam_obj, base.t_cam_obj) and np.array_equal(f64.code, base.code)
+    assert opt.reconstruct_objects([]) == []
+    assert not opt.reconstruct_object(d["t_cam_obj"], np.zeros((0, 3), np.float32), d["rays"], d["depth"]).is_good
+    assert not opt.reconstruct_object(d["t_cam_obj"], np.full_like(d["pts"], np.nan), d["rays"], d["depth"]).is_good
+    assert not opt.reconstruct_object(np.full((4, 4), np.nan, np.float32), d["pts"], d["rays"], d["depth"]).is_good
+    long_code = opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"], np.zeros(100, np.float32))
+    assert long_code.is_good and long_code.code.shape == (64,)
+    T = np.eye(4, dtype=np.float32)
+    T[2, 3] = 10.0
+    out = opt.estimate_poses_cam_obj([(T, 2.0, np.zeros((0, 3), np.float32), np.zeros(64, np.float32)),
+                                      (d["t_cam_obj"] / np.float32(1), 2.0, d["pts"], np.zeros(64, np.float32))])
+    assert out.shape == (2, 4, 4) and np.isnan(out[0]).all() and np.isfinite(out[1]).all()
+    assert opt.estimate_poses_cam_obj([]).shape == (0, 4, 4)
+    assert np.isnan(opt.compute_sdf_loss_objectpoint_zhjd(np.zeros((0, 3), np.float32), np.zeros(64, np.float32)))
