@@ -18,6 +18,9 @@
       chunks of 64^3, `no_grad` forward for decode_sdf - loss_utils.py:51-79; forward + one reverse-mode pass with a
       ones cotangent for get_batch_sdf_jacobian - loss_utils.py:82-113; weight-norm hooks active, TF32 off), next to
       this library's kernels on the same rows.  A port of the query pattern, not the reference's files.
+  torchgn the whole-object counterpart of torchq: `tools/torch_gn.py` (a stock-PyTorch FP32 port of
+      `reconstruct_object`, every tensor on the B200, one detection at a time like the reference) on C1- and C2-shaped
+      detections, next to this library on the same detections.
 All times are device-synchronised wall times of the public API calls (max over ranks)."""
 import json
 import os
@@ -227,6 +230,31 @@ if "torchq" in sys.argv[1:] and world == 1:
          forward_speedup=t_tf / t_of, jacobian_speedup=t_tj / t_oj,
          max_abs_sdf_diff=float((s_t - s_o).abs().max()),
          jac_rms_diff=float(((j_t.squeeze(1) - j_o) ** 2).mean().sqrt()))
+
+if "torchgn" in sys.argv[1:] and world == 1:
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import torch_gn
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    net = synth.load_wfit().cuda().eval()
+    cfg = synth.kitti_config()
+    opt = Optimizer(dec, cfg, mode="tc", device=local)
+    for name, M, n_obj in (("C1", 250, 8), ("C2", 2048, 8)):
+        dets = [synth.make_kitti_detection(k, M=M, n_bg=200) for k in range(n_obj)]
+
+        def torch_all():
+            return [torch_gn.reconstruct_object(net, cfg, d["t_cam_obj"], d["pts"], d["rays"], d["depth"]) for d in dets]
+
+        t_t, res_t = timed(torch_all, reps=2, warm=1)
+        t_o, res_o = timed(lambda: opt.reconstruct_objects(dets), reps=5)
+        t_o1, _ = timed(lambda: [opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"]) for d in dets], reps=3)
+        errs = [synth.pose_errors(a[0].cpu().numpy(), b.t_cam_obj) for a, b in zip(res_t, res_o) if a[2] and b.is_good]
+        emit(config="%s-shaped detections (%d surface pts, %d rays x 50 samples, 10 GN iters): stock PyTorch FP32 port "
+                    "of reconstruct_object on the same B200, one detection at a time, vs this library" % (name, M, M + 200),
+             objects=n_obj, torch_objects_per_s=n_obj / t_t, ours_batched_objects_per_s=n_obj / t_o,
+             ours_one_at_a_time_objects_per_s=n_obj / t_o1, speedup_batched=t_t / t_o, speedup_one_at_a_time=t_t / t_o1,
+             good_torch=sum(1 for a in res_t if a[2]), good_ours=sum(1 for b in res_o if b.is_good),
+             max_translation_diff_m=max(e[0] for e in errs), max_rotation_diff_deg=max(e[1] for e in errs))
 
 if world > 1:
     dist.destroy_process_group()
