@@ -11,6 +11,7 @@
 #include "kernels.h"
 #include "kernels_tc.h"
 #include "frame.h"
+#include "posegraph.h"
 
 using namespace dsp;
 
@@ -581,6 +582,40 @@ int dspslam_frame_build_mono(dspslam_handle* h, void* stream, const dspslam_fram
     if (rc) return rc;
     const int nl = launch_frame_mono(d, masks, n_masks, bboxes, rays_out, info_out, h->ws, S(stream));
     return check_launch(h, nl, "dspslam_frame_build_mono");
+}
+
+int dspslam_pg_from_matrices(dspslam_handle* h, void* stream, const float* T, int n, double* poses_out) {
+    if (!h || (n > 0 && (!T || !poses_out))) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (n < 0) return fail(DSPSLAM_E_BADARG, "negative count");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return check_launch(h, launch_pg_from_matrices(T, n, poses_out, S(stream)), "dspslam_pg_from_matrices");
+}
+
+int dspslam_pg_linearize(dspslam_handle* h, void* stream, const double* vertices, int n_vertices,
+                         const int32_t* edge_i, const int32_t* edge_j, const double* measurements, int n_edges,
+                         double inv_sigma, double huber_delta, double* error, double* Ji, double* Jj, double* chi2,
+                         double* rho, double* weight, double* A, double* b, double* Hij) {
+    if (!h) return fail(DSPSLAM_E_BADARG, "null handle");
+    if (n_vertices < 0 || n_edges < 0) return fail(DSPSLAM_E_BADARG, "negative count");
+    if (n_edges > 0 && (!vertices || !edge_i || !edge_j || !measurements || !error || !Ji || !Jj || !chi2 || !rho ||
+                        !weight))
+        return fail(DSPSLAM_E_BADARG, "null argument");
+    if ((A == nullptr) != (b == nullptr)) return fail(DSPSLAM_E_BADARG, "A and b go together");
+    if (!(inv_sigma > 0.0)) return fail(DSPSLAM_E_BADARG, "inv_sigma must be positive");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    const int nl = launch_pg_linearize(vertices, n_vertices, edge_i, edge_j, measurements, n_edges, inv_sigma,
+                                       huber_delta, error, Ji, Jj, chi2, rho, weight, A, b, Hij, S(stream));
+    return check_launch(h, nl, "dspslam_pg_linearize");
+}
+
+int dspslam_pg_oplus(dspslam_handle* h, void* stream, double* vertices, const double* updates, int n) {
+    if (!h || (n > 0 && (!vertices || !updates))) return fail(DSPSLAM_E_BADARG, "null argument");
+    if (n < 0) return fail(DSPSLAM_E_BADARG, "negative count");
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    return check_launch(h, launch_pg_oplus(vertices, updates, n, S(stream)), "dspslam_pg_oplus");
 }
 
 int dspslam_profile_enable(dspslam_handle* h, int on) {

@@ -22,6 +22,7 @@ EXPORTS = [
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
     "dspslam_marching_cubes", "dspslam_frame_build_kitti", "dspslam_frame_build_mono",
+    "dspslam_pg_from_matrices", "dspslam_pg_linearize", "dspslam_pg_oplus",
 ]
 FRAME_INFO = 8
 FRAME_MAX_DETS = 256
@@ -109,6 +110,13 @@ def lib():
                                             fp, C.c_int, fp, fp, fp, fp, fp, fp, fp, fp]
     L.dspslam_frame_build_mono.restype = C.c_int
     L.dspslam_frame_build_mono.argtypes = [vp, vp, C.POINTER(FrameParams), fp, C.c_int, fp, fp, fp]
+    L.dspslam_pg_from_matrices.restype = C.c_int
+    L.dspslam_pg_from_matrices.argtypes = [vp, vp, fp, C.c_int, fp]
+    L.dspslam_pg_linearize.restype = C.c_int
+    L.dspslam_pg_linearize.argtypes = [vp, vp, fp, C.c_int, fp, fp, fp, C.c_int, C.c_double, C.c_double,
+                                       fp, fp, fp, fp, fp, fp, fp, fp, fp]
+    L.dspslam_pg_oplus.restype = C.c_int
+    L.dspslam_pg_oplus.argtypes = [vp, vp, fp, fp, C.c_int]
     if L.dspslam_abi_version() != ABI_VERSION:
         raise NativeError("libdspslam_sm100.so ABI version mismatch")
     _lib = L

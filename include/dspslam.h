@@ -17,6 +17,11 @@
  *                                      FrameWithLiDAR.get_detections: LiDAR crop, sub-sampling, mask association,
  *                                      background pixels, rays - output in the batch layout of dspslam_gn_joint
  *   dspslam_frame_build_mono           reconstruct/mono_sequence.py:95-106  background rays of the largest mask
+ *   dspslam_pg_from_matrices           src/Converter.cc:37-54              Converter::toSE3Quat
+ *   dspslam_pg_linearize               include/ObjectPoseGraph.h:56-88     EdgeSE3LieAlgebra::computeError / linearizeOplus,
+ *                                      chi2 + Huber + quadratic form as g2o applies them to these edges
+ *                                      (src/Optimizer_util.cc:199-225, 555-583, 647-656, 701-711)
+ *   dspslam_pg_oplus                   g2o VertexSE3Expmap::oplusImpl (Thirdparty/g2o/g2o/types/types_six_dof_expmap.h:73-76)
  *
  * Conventions
  *   - plain C types only; all array arguments are DEVICE pointers unless the name
@@ -216,6 +221,28 @@ int dspslam_frame_build_kitti(dspslam_handle* h, void* stream, const dspslam_fra
 int dspslam_frame_build_mono(dspslam_handle* h, void* stream, const dspslam_frame_params* prm,
                              const uint8_t* masks, int n_masks, const float* bboxes, float* rays_out,
                              int32_t* info_out);
+
+/* ---- camera-object pose-graph edges (the consumer of the SE(3) measurement of dspslam_gn_pose_only) ----------
+ * All arrays FP64 on the device.  A pose is g2o's Vector7d: (tx, ty, tz, qx, qy, qz, qw), w >= 0, unit norm. */
+
+/* T[n][16] row-major FP32 4x4 -> poses_out[n][7] (Converter::toSE3Quat: double R, t -> SE3Quat(R, t)). */
+int dspslam_pg_from_matrices(dspslam_handle* h, void* stream, const float* T, int n, double* poses_out);
+
+/* For every edge e between vertices[edge_i[e]] (keyframe, T_cw) and vertices[edge_j[e]] (object, T_ow) with
+ * measurement measurements[e] (T_co):
+ *   error[e][6]  = log(Tij^-1 Ti Tj^-1)  (omega, upsilon)          Ji[e][6][6], Jj[e][6][6] row-major
+ *   chi2[e]      = error^T (inv_sigma I) error                     rho[e], weight[e] = Huber rho, rho'
+ *                  (huber_delta <= 0: no robust kernel, rho = chi2, weight = 1)
+ * and, when A and b are given (both or neither; Hij optional), g2o's quadratic form with the robust information
+ * weight * inv_sigma * I:  A[v][6][6] = sum J^T W J,  b[v][6] = sum J^T (-W error) over the edges of vertex v in edge
+ * order,  Hij[e][6][6] = Ji^T W Jj.  n_edges = 0 is allowed (A, b are zero-filled). */
+int dspslam_pg_linearize(dspslam_handle* h, void* stream, const double* vertices, int n_vertices,
+                         const int32_t* edge_i, const int32_t* edge_j, const double* measurements, int n_edges,
+                         double inv_sigma, double huber_delta, double* error, double* Ji, double* Jj, double* chi2,
+                         double* rho, double* weight, double* A, double* b, double* Hij);
+
+/* vertices[v] <- exp(updates[v]) * vertices[v], updates[n][6] = (omega, upsilon). */
+int dspslam_pg_oplus(dspslam_handle* h, void* stream, double* vertices, const double* updates, int n);
 
 #ifdef __cplusplus
 }
