@@ -42,6 +42,7 @@ struct DecoderDev {
     // tcgen05 path (kernels_tc.cu); null until packed
     const uint8_t* tc_blob;  // FP16 weight stage images (forward program, then backward program)
     uint8_t* tc_xtra1;       // extras record (layers 0 and 4) of the single-code entry points
+    float* tc_park;          // per-CTA scratch of the Jacobian kernels: layer-4 input gradients, [cta][128][68]
 };
 
 // Per-object Gauss-Newton state (one per detection in the batch).

@@ -41,6 +41,8 @@ constexpr int A_BYTES = 8 * A_BLK;
 constexpr int AX_BYTES = 4096;     // the K=16 extra block of the tile: 128 rows x 32 B, no swizzle
 constexpr int STAGE_BYTES = 16384;
 constexpr int JLD = 76;            // row stride (floats) of the per-row Jacobian buffer (float4-aligned rows)
+constexpr int PARK_LD = 68;        // row stride (floats) of the layer-4 input-gradient park in global memory
+constexpr int PARK_CTAS = 256;     // CTAs the park is sized for (grids are capped at the SM count)
 constexpr float GSCALE = 256.f;    // gradients are carried scaled so that FP16 keeps them normal
 constexpr int MAX_PROG = 256;
 constexpr int TMEM_COLS = 512;
@@ -97,7 +99,7 @@ template <int MODE>
 struct Cfg {
     static constexpr bool JAC = MODE >= 4;
     static constexpr bool GN = (MODE == 3 || MODE == 5);
-    static constexpr int NST = JAC ? 3 : 5;
+    static constexpr int NST = 5;
     static constexpr int O_AX = A_BYTES;
     static constexpr int O_ST = O_AX + AX_BYTES;
     static constexpr int O_W8 = O_ST + NST * STAGE_BYTES;
@@ -105,8 +107,9 @@ struct Cfg {
     static constexpr int O_PART = O_XYZ + 2048;
     static constexpr int O_DY = O_PART + 1024;
     static constexpr int O_BAR = O_DY + 512;
-    static constexpr int O_JROW = O_BAR + 256;
-    static constexpr int O_WROW = O_JROW + (JAC ? TILE_M * JLD * 4 : 0);
+    // the per-row Jacobian buffer (TILE_M x JLD floats) lives at offset 0, over the activation tile, which is dead
+    // once the last backward MMA has completed and is not written again before the tile's J^T J is done
+    static constexpr int O_WROW = O_BAR + 256;
     static constexpr int O_RT = O_WROW + (JAC ? 512 : 0);
     static constexpr int O_END = O_RT + (JAC ? 512 : 0);
     static constexpr int SMEM = O_END + 1024;   // + alignment slack
@@ -148,7 +151,8 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     auto bar_empty = [&](int s) { return bar0 + 8u * (NST + s); };
     const uint32_t bar_aready = bar0 + 8u * (2 * NST), bar_dfull = bar0 + 8u * (2 * NST + 1);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + C::O_BAR + 8 * (2 * NST + 2));
-    float* jrow = reinterpret_cast<float*>(sm + C::O_JROW);
+    float* jrow = reinterpret_cast<float*>(sm);
+    static_assert(TILE_M * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the activation tile");
     float* wrows = reinterpret_cast<float*>(sm + C::O_WROW);
     float* rts = reinterpret_cast<float*>(sm + C::O_RT);
 
@@ -273,6 +277,8 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         uint32_t dph = 0;
         uint32_t mw[8][8];                                 // ReLU sign words of this thread's 256 columns, per layer
         const int L = a.dec.L;
+        // layer-4 input gradients of row r wait here (written and read back by the hc == 1 thread of the row)
+        float* park = JAC ? a.dec.tc_park + ((size_t)blockIdx.x * TILE_M + r) * PARK_LD : nullptr;
 
         auto signal_ready = [&]() {
             tc_fence_before();
@@ -458,7 +464,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         const uint32_t m = mw[l - 1][j];
                         if (split && col >= h3p) {           // pure input-gradient columns
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) jrow[r * JLD + (col + i - h3)] = __uint_as_float(v[i]);
+                            for (int i = 0; i < 32; ++i) park[col + i - h3] = __uint_as_float(v[i]);
                             continue;
                         }
                         uint32_t p[16];
@@ -466,7 +472,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
 #pragma unroll
                             for (int i = 0; i < 32; ++i) {
                                 const bool hid = (col + i) < h3;
-                                if (!hid) jrow[r * JLD + (col + i - h3)] = __uint_as_float(v[i]);
+                                if (!hid) park[col + i - h3] = __uint_as_float(v[i]);
                                 if (!hid || !((m << i) & 0x80000000u)) v[i] = 0u;
                             }
                         } else {
@@ -487,7 +493,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 dph ^= 1u;
                 tc_fence_after();
                 const float inv_s = 1.f / GSCALE;
-                if (hc == 0) {
+                if (hc == 1) {                                // the thread that parked the row's layer-4 gradients
                     uint32_t v0[32], v1[32], v2[32];
                     tmem_ld32(trow + 0, v0);
                     tmem_ld32(trow + 32, v1);
@@ -497,12 +503,12 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     if (MODE == 4) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
-                            if (i < L + 3) jr[i] = (__uint_as_float(v0[i]) + jr[i]) * inv_s;
-                            if (32 + i < L + 3) jr[32 + i] = (__uint_as_float(v1[i]) + jr[32 + i]) * inv_s;
-                            if (64 + i < L + 3) jr[64 + i] = (__uint_as_float(v2[i]) + jr[64 + i]) * inv_s;
+                            if (i < L + 3) jr[i] = (__uint_as_float(v0[i]) + park[i]) * inv_s;
+                            if (32 + i < L + 3) jr[32 + i] = (__uint_as_float(v1[i]) + park[32 + i]) * inv_s;
+                            if (64 + i < L + 3) jr[64 + i] = (__uint_as_float(v2[i]) + park[64 + i]) * inv_s;
                         }
                     } else {
-                        // J row = [pose 7 | code L] in place over gin: read the xyz part first, then descend
+                        // J row = [pose 7 | code L]
                         auto dval = [&](int i) -> float {
                             return __uint_as_float(i < 32 ? v0[i & 31] : (i < 64 ? v1[i & 31] : v2[i & 31]));
                         };
@@ -511,13 +517,13 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         for (int c = 0; c < 3; ++c) gxyz[c] = 0.f;
 #pragma unroll
                         for (int i = 0; i < 96; ++i) {
-                            if (i >= L && i < L + 3) gxyz[i - L] = (dval(i) + jr[i]) * inv_s;
+                            if (i >= L && i < L + 3) gxyz[i - L] = (dval(i) + park[i]) * inv_s;
                         }
                         const float4 pc = xyzs[r];
                         const float cf = pc.w;
 #pragma unroll
                         for (int i = 95; i >= 0; --i) {
-                            if (i < L) jr[POSE + i] = cf * (dval(i) + jr[i]) * inv_s;
+                            if (i < L) jr[POSE + i] = cf * (dval(i) + park[i]) * inv_s;
                         }
                         build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
                         for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;    // padding columns of the 4x4 blocks
@@ -785,7 +791,8 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
 
     // device: [weight images | one extras record for the single-code entry points]
     const size_t wbytes = (B.bytes.size() + 255) & ~(size_t)255;
-    const size_t total = wbytes + 2 * XTRA_BYTES;
+    const size_t park_bytes = (size_t)PARK_CTAS * TILE_M * PARK_LD * sizeof(float);
+    const size_t total = wbytes + 2 * XTRA_BYTES + park_bytes;
     uint8_t* dev = nullptr;
     cudaError_t e = cudaMalloc(&dev, total);
     if (e != cudaSuccess) { g_tc_err = cudaGetErrorString(e); return 2; }
@@ -809,6 +816,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     *hblob = reinterpret_cast<__half*>(dev);
     dec.tc_blob = dev;
     dec.tc_xtra1 = dev + wbytes;
+    dec.tc_park = reinterpret_cast<float*>(dev + wbytes + 2 * XTRA_BYTES);
     return 0;
 }
 
@@ -842,7 +850,7 @@ int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int
     a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
     a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
     a.n_tiles = (int)((n + TILE_M - 1) / TILE_M);
-    launch_tc<4>(a, std::min(a.n_tiles, sm_count), st);
+    launch_tc<4>(a, std::min(std::min(a.n_tiles, sm_count), PARK_CTAS), st);
     return 2;
 }
 
@@ -860,7 +868,7 @@ int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
-    launch_tc<5>(a, sm_count, st);
+    launch_tc<5>(a, std::min(sm_count, PARK_CTAS), st);
     return 1;
 }
 
