@@ -240,6 +240,9 @@ __global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __rest
 // Phase 0 ends two samples behind the previous iteration's first hit (or at the middle of the in-ball
 // interval when there is no history), the next phases take 4, 8, ... samples and the last one the rest.
 // ---------------------------------------------------------------------------
+#ifndef DSP_HIT_MARGIN
+#define DSP_HIT_MARGIN 3   // phase 0 ends this many samples behind the previous iteration's first closing sample
+#endif
 __global__ void __launch_bounds__(256) k_gn_sample(GnWork w) {
     __shared__ int s_obj, s_cnt, s_nv, s_base;
     const int tid = threadIdx.x;
@@ -282,7 +285,7 @@ __global__ void __launch_bounds__(256) k_gn_sample(GnWork w) {
             start = j_lo; end = j_hi;
             if (P > 1) {
                 const int pred = w.ray_hit[warp];
-                int e = (pred < 0) ? j_lo + (j_hi - j_lo + 1) / 2 : min(j_hi, pred + 3);
+                int e = (pred < 0) ? j_lo + (j_hi - j_lo + 1) / 2 : min(j_hi, pred + DSP_HIT_MARGIN);
                 e = max(e, min(j_hi, j_lo + 1));
                 int st = j_lo;
                 for (int p = 1; p <= ph; ++p) {
