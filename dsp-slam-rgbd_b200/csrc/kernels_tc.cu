@@ -95,11 +95,18 @@ struct TcArgs {
     GnWork w;
 };
 
+#ifndef DSP_TC_PAIR
+#define DSP_TC_PAIR 1
+#endif
+
 template <int MODE>
 struct Cfg {
     static constexpr bool JAC = MODE >= 4;
     static constexpr bool GN = (MODE == 3 || MODE == 5);
     static constexpr int NST = 5;
+    // forward-only variants run as clusters of two CTAs that walk the same weight sequence: every hidden stage is
+    // fetched from L2 once per pair (each CTA issues one half, multicast to both), halving the L2 -> SM traffic
+    static constexpr bool PAIR = DSP_TC_PAIR && !JAC;
     static constexpr int O_AX = A_BYTES;
     static constexpr int O_ST = O_AX + AX_BYTES;
     static constexpr int O_W8 = O_ST + NST * STAGE_BYTES;
@@ -135,6 +142,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     using C = Cfg<MODE>;
     constexpr bool JAC = C::JAC;
     constexpr int NST = C::NST;
+    constexpr bool PAIR = C::PAIR;
     extern __shared__ uint8_t smem_raw[];
     const uint32_t raw = smem_u32(smem_raw);
     const uint32_t sbase = (raw + 1023u) & ~1023u;
@@ -157,7 +165,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     float* rts = reinterpret_cast<float*>(sm + C::O_RT);
 
     if (tid == 0) {
-        for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+        for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), PAIR ? 2 : 1); }
         mbar_init(bar_aready, 8);
         mbar_init(bar_dfull, 1);
         fence_mbar_init();
@@ -170,16 +178,22 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (PAIR) cluster_sync_all();                           // the peer's barriers exist before anything is sent to them
     const uint32_t tmem = *tmem_slot;
 
     int n_tiles = a.n_tiles;
     if (C::GN) n_tiles = a.w.n_tiles[MODE == 3 ? 0 : 1];
     constexpr int NPROG = JAC ? 2 : 1;
+    // tile walk: a pair takes tiles (tb, tb + 1); both CTAs make the same number of trips (the multicast protocol
+    // needs them in step), a CTA whose tile index falls behind the list runs the trip with no valid rows
+    const int rank = PAIR ? (int)(blockIdx.x & 1u) : 0;
+    const int tb0 = (int)blockIdx.x - rank;
 
     if (warp == 8) {
         // ===================== weight producer (whole warp, one elected lane issues) =====================
         uint32_t s = 0, ph = 0;
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int tb = tb0; tb < n_tiles; tb += gridDim.x) {
+            const int t = min(tb + rank, n_tiles - 1);
             const int obj = C::GN ? a.w.tile_obj[t] : 0;
             const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
             for (int p = 0; p < NPROG; ++p) {
@@ -204,7 +218,12 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                             mbar_wait(bar_empty(s), ph ^ 1u);
                             if (elect_one()) {
                                 mbar_expect_tx(bar_full(s), bytes);
-                                bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                                if (PAIR) {
+                                    const uint32_t half = bytes >> 1;
+                                    bulk_g2s_mc(sST + s * STAGE_BYTES + rank * half, src + rank * half, half, bar_full(s), 3);
+                                } else {
+                                    bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                                }
                             }
                             __syncwarp();
                             src += bytes;
@@ -214,6 +233,12 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 }
             }
         }
+        if (PAIR) {                                         // tail: every arrive the peer still owes this CTA has landed
+            for (int i = 0; i < NST; ++i) {
+                mbar_wait(bar_empty(s), ph ^ 1u);
+                if (++s == NST) { s = 0; ph ^= 1u; }
+            }
+        }
     } else if (warp == 9) {
         // ===================== MMA issuer (whole warp, one elected lane issues) =====================
         uint32_t s = 0, ph = 0, aph = 0;
@@ -221,7 +246,10 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         const uint64_t bdesc0 = smem_desc(sST, 16, 512, 4);      // weight stage: 64B swizzle, 8-row groups 512 B apart
         const uint64_t axdesc = smem_desc(sAX, 128, 256, 0);
         const uint64_t bxdesc0 = smem_desc(sST, 128, 256, 0);
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        auto release = [&](uint32_t bar) {                   // stage reusable (in both CTAs of a pair) once these MMAs finish
+            if (PAIR) umma_commit_mc(bar, 3); else umma_commit(bar);
+        };
+        for (int tb = tb0; tb < n_tiles; tb += gridDim.x) {
             for (int p = 0; p < NPROG; ++p) {
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
@@ -237,7 +265,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                                 const int nn = min(256, (int)ld.n - n0);
                                 umma_f16(tmem + n0, axdesc, bx + (uint64_t)((n0 * 32) >> 4), idesc_f16(TILE_M, nn), 0u);
                             }
-                            umma_commit(bar_empty(s));
+                            release(bar_empty(s));
                         }
                         __syncwarp();
                         if (++s == NST) { s = 0; ph ^= 1u; }
@@ -255,7 +283,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                                 const uint64_t bd = bdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
                                 umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && kc == 0) ? 0u : 1u);
                                 umma_f16(dcol, ad + 2, bd + 2, id, 1u);
-                                umma_commit(bar_empty(s));       // stage reusable once these MMAs finish
+                                release(bar_empty(s));
                             }
                             __syncwarp();
                             if (++s == NST) { s = 0; ph ^= 1u; }
@@ -295,7 +323,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 st_shared_v4(blk + (uint32_t)(((cc0 + qq) ^ rx) << 4), p[4 * qq], p[4 * qq + 1], p[4 * qq + 2], p[4 * qq + 3]);
         };
 
-        for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        for (int tb = tb0; tb < n_tiles; tb += gridDim.x) {
+            const bool idle = tb + rank >= n_tiles;        // (pairs only) the odd CTA's trip behind the last tile
+            const int t = idle ? n_tiles - 1 : tb + rank;
             // ---------------- tile rows ----------------
             int obj = 0, row0 = 0, rows_valid = 0;
             int dest = -1;
@@ -305,7 +335,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             size_t jb = 0;
             if (MODE == 3) {
                 obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
-                rows_valid = min(TILE_M, a.w.st[obj].ph_rows[a.w.phase] - row0);
+                rows_valid = idle ? 0 : min(TILE_M, a.w.st[obj].ph_rows[a.w.phase] - row0);
             } else if (MODE == 5) {
                 obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
                 M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
@@ -314,7 +344,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 jb = (size_t)a.w.pts_off[obj] + (size_t)a.w.ray_off[obj] * a.w.prm.D;
             } else {
                 const int64_t left = a.n - (int64_t)t * TILE_M;
-                rows_valid = (int)(left < TILE_M ? left : TILE_M);
+                rows_valid = idle ? 0 : (int)(left < TILE_M ? left : TILE_M);
             }
             if (hc == 0) {
                 float x = 0.f, y = 0.f, z = 0.f;
@@ -636,6 +666,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     // ---------------- teardown ----------------
     tc_fence_before();
     __syncthreads();
+    if (PAIR) cluster_sync_all();                           // neither CTA leaves while the other may still signal it
     if (warp == 9) {
         __syncwarp();
         tc_fence_after();
@@ -823,7 +854,21 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
 namespace {
 template <int MODE>
 void launch_tc(const tc::TcArgs& a, int grid, cudaStream_t st) {
-    tc::k_tc<MODE><<<grid, tc::NT, tc::Cfg<MODE>::SMEM, st>>>(a);
+    if (!tc::Cfg<MODE>::PAIR) {
+        tc::k_tc<MODE><<<grid, tc::NT, tc::Cfg<MODE>::SMEM, st>>>(a);
+        return;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)((grid + 1) & ~1), 1, 1);  // whole pairs; the odd CTA of the last pair may idle
+    cfg.blockDim = dim3(tc::NT, 1, 1);
+    cfg.dynamicSmemBytes = tc::Cfg<MODE>::SMEM;
+    cfg.stream = st;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = 2; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, tc::k_tc<MODE>, a);
 }
 }  // namespace
 
