@@ -673,6 +673,15 @@ __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int l
         for (int e = tid; e < n * n + n; e += SOLVE_NT) {
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
             int g = 0;
+            for (; g + 16 <= ng; g += 16) {                     // 16 loads in flight, same order of additions as below
+                float v[16];
+#pragma unroll
+                for (int u = 0; u < 16; ++u) v[u] = part[(size_t)(g + u) * PART_STRIDE + e];
+#pragma unroll
+                for (int u = 0; u < 16; u += 4) {
+                    a0 += (double)v[u]; a1 += (double)v[u + 1]; a2 += (double)v[u + 2]; a3 += (double)v[u + 3];
+                }
+            }
             for (; g + 4 <= ng; g += 4) {                       // fixed summation order: ((g0+g4+..)+(g1+..))+...
                 a0 += (double)part[(size_t)(g + 0) * PART_STRIDE + e];
                 a1 += (double)part[(size_t)(g + 1) * PART_STRIDE + e];
