@@ -104,9 +104,10 @@ struct Cfg {
     static constexpr bool JAC = MODE >= 4;
     static constexpr bool GN = (MODE == 3 || MODE == 5);
     static constexpr int NST = 5;
-    // forward-only variants run as clusters of two CTAs that walk the same weight sequence: every hidden stage is
-    // fetched from L2 once per pair (each CTA issues one half, multicast to both), halving the L2 -> SM traffic
-    static constexpr bool PAIR = DSP_TC_PAIR && !JAC;
+    // the kernel runs as clusters of two CTAs that walk the same weight sequence: every hidden stage is fetched from
+    // L2 once per pair (each CTA issues one half, multicast to both), halving the L2 -> SM traffic
+    // (DSP_TC_PAIR: 0 = never, 1 = forward-only variants, 2 = all variants)
+    static constexpr bool PAIR = DSP_TC_PAIR == 2 || (DSP_TC_PAIR == 1 && !JAC);
     static constexpr int O_AX = A_BYTES;
     static constexpr int O_ST = O_AX + AX_BYTES;
     static constexpr int O_W8 = O_ST + NST * STAGE_BYTES;
@@ -340,7 +341,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 obj = a.w.tile_obj[t]; row0 = a.w.tile_row0[t];
                 M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
                 const int K = a.w.prm.pose_only ? 0 : a.w.st[obj].K;
-                rows_valid = min(TILE_M, M_obj + K - row0);
+                rows_valid = idle ? 0 : min(TILE_M, M_obj + K - row0);
                 jb = (size_t)a.w.pts_off[obj] + (size_t)a.w.ray_off[obj] * a.w.prm.D;
             } else {
                 const int64_t left = a.n - (int64_t)t * TILE_M;
@@ -604,7 +605,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     const int nb = (n + 3) >> 2;
                     const int nblk = nb * (nb + 1) / 2;
                     float* part = w.partials + ((size_t)obj * w.jgroups_max + (row0 / GROUP_ROWS)) * PART_STRIDE;
-                    if (etid < nblk) {
+                    if (idle) {
+                        // (pairs) trip behind the last tile: nothing to reduce, nothing to store
+                    } else if (etid < nblk) {
                         int bi = 0, rem = etid;                  // block (bi, bj), bi <= bj, row-major over the upper triangle
                         while (rem >= nb - bi) { rem -= nb - bi; ++bi; }
                         const int bj = bi + rem;
@@ -653,7 +656,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         if (lane == 0) { parts[q] = ls; parts[4 + q] = lr; }
                     }
                     named_bar_sync(1, EPI_THREADS);
-                    if (etid == 0) {
+                    if (etid == 0 && !idle) {
                         part[PART_LOSS] = parts[0] + parts[1] + parts[2] + parts[3];
                         part[PART_LOSS + 1] = parts[4] + parts[5] + parts[6] + parts[7];
                     }
