@@ -286,10 +286,10 @@ def ours_arm(args, rank, world, local_rank):
         "roofline": {"bound": "tensor", "kernel": "forward-only decoder over in-ball ray samples (GN render term)",
                      "achieved": fwd_tf, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": fwd_tf / pk["tflops"],
                      # DRAM bytes of one forward launch (read + write) from the committed `ncu --set full` capture of
-                     # this command: profiles/r01_ncu_full_bench_k_tc_v4_summary.txt (weights + 16 B per sample in,
+                     # this command: profiles/r01_ncu_full_bench_k_tc_pair_summary.txt (weights + 16 B per sample in,
                      # 4 B out; activations never leave the SM)
-                     "traffic": (16739840 + 13568) if args.mode == "tc" else None,
-                     "traffic_source": "profiles/r01_ncu_full_bench_k_tc_v4_summary.txt (dram__bytes_read+write.sum)",
+                     "traffic": (16552960 + 0) if args.mode == "tc" else None,
+                     "traffic_source": "profiles/r01_ncu_full_bench_k_tc_pair_summary.txt (dram__bytes_read+write.sum)",
                      "peak_source": pk["src"],
                      "avg_launch_ms": prof["ms_gn_fwd"] / max(1, prof["n_gn_fwd"]),
                      "rows_per_launch": prof["rows_gn_fwd"] / max(1, prof["n_gn_fwd"]),
