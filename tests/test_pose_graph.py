@@ -193,6 +193,23 @@ def test_gpu_linearize_matches_restatement(graph_cls, seed, huber):
 
 
 @pytest.mark.gpu
+def test_gpu_quadratic_form_across_edge_chunks(graph_cls):
+    """5 000 edges: the per-vertex gather walks the edge list in chunks of 2 048 with one warp per half chunk; the
+    sums must still be the edge-order sums of the restatement (and identical from run to run)."""
+    verts, ei, ej, meas, _ = _random_graph(12, n_kf=60, n_obj=40, n_edges=5000)
+    g = graph_cls(inv_sigma=1e3, huber_delta=10.0)
+    g.set_vertices(verts)
+    g.set_edges(ei, ej, meas)
+    lin = g.linearize()
+    o = pg.linearize(verts, ei, ej, meas, 1e3, 10.0)
+    A, b = lin.A.cpu().numpy(), lin.b.cpu().numpy()
+    assert np.abs(A - o["A"]).max() <= TOL * np.abs(o["A"]).max()
+    assert np.abs(b - o["b"]).max() <= TOL * np.abs(o["b"]).max()
+    again = g.linearize()
+    assert np.array_equal(again.A.cpu().numpy(), A) and np.array_equal(again.b.cpu().numpy(), b)
+
+
+@pytest.mark.gpu
 def test_gpu_oplus_and_empty_graph(graph_cls):
     rng = np.random.default_rng(10)
     verts = np.array([_rand_pose(rng) for _ in range(17)])
