@@ -331,6 +331,27 @@ def test_c2_sized_batch_tc_vs_fp32(eng):
         assert dt < 1e-2 and ang < 0.1
 
 
+def test_c2_sized_object_fp32_vs_oracle(eng, odec):
+    """One GN step of a C2-sized detection (2 048 surface points + a few thousand render rows = ~40 row groups, so the
+    partial reduction of the solve kernel takes its 16-wide path) against the oracle's H, b and updated pose."""
+    from oracle import dspslam_oracle as orc
+    from dspslam import synth
+    cfg = synth.kitti_config()
+    cfg.optimizer.joint_optim.num_iterations = 1
+    d = synth.make_kitti_detection(1, M=2048, n_bg=200)
+    res = eng.gn_joint([d], params(cfg, iters=1), mode="fp32", debug=True)
+    trace = []
+    o = orc.OracleOptimizer(odec, cfg).reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"], trace=trace)
+    dbg = res.dbg[0, 0]
+    H, b = dbg[:5041].reshape(71, 71), dbg[5041:5112]
+    assert res.status[0] == 0 and o["is_good"]
+    assert abs(int(dbg[5112]) - int(trace[0]["K"])) <= 2 and int(trace[0]["K"]) + 2048 > 16 * 128
+    assert np.linalg.norm(H - trace[0]["H"]) / np.linalg.norm(trace[0]["H"]) < 1e-3
+    assert np.linalg.norm(b - trace[0]["b"]) / np.linalg.norm(trace[0]["b"]) < 1e-3
+    dt, ang, _ = synth.pose_errors(res.t_cam_obj[0], o["t_cam_obj"])
+    assert dt < 1e-3 and ang < 1e-2
+
+
 def test_grid_sharded_equals_single(eng):
     """dspslam.dist.grid_sdf_sharded (world size 1 here; tools/dist_check.py runs it under torchrun + NCCL)."""
     import torch
