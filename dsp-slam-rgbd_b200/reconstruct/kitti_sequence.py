@@ -79,22 +79,35 @@ class FrameWithLiDAR:
 
 class KITIISequence:
     def __init__(self, data_dir, configs, engine=None, decoder=None):
-        """`engine`: a dspslam.engine.Engine; or pass the `decoder` module the Optimizer uses (the engine is shared)."""
+        """Reference signature `KITIISequence(data_dir, configs)` (`kitti_sequence.py:219-238`, called through
+        `reconstruct.get_sequence` from `src/System.cc:99`).  Optional: `engine` (a dspslam.engine.Engine) or the
+        `decoder` module the Optimizer uses; with neither, the engine is resolved at the first frame - the one the
+        process's Optimizer already created, else one built from `get_decoder(configs)` (cached per DeepSDF_DIR, so
+        it is the module `src/System.cc:98` holds)."""
         self.root_dir = data_dir
         self.rgb_dir = os.path.join(data_dir, "image_2")
         self.velo_dir = os.path.join(data_dir, "velodyne")
         self.calib_file = os.path.join(data_dir, "calib.txt")
         self.load_calib()
         self.configs = configs
-        self.online = False
+        self.num_frames = len(os.listdir(self.rgb_dir)) if os.path.isdir(self.rgb_dir) else 0
+        self.online = self.configs.detect_online
         self.lbl2d_dir = self.configs.path_label_2d
         self.lbl3d_dir = self.configs.path_label_3d
-        if engine is None:
-            from reconstruct.optimizer import _engine_for
-            engine = _engine_for(decoder)
-        self.engine = engine
+        if not self.online:
+            assert self.lbl2d_dir is not None and self.lbl3d_dir is not None, "pre-stored label paths missing"
+        from reconstruct import get_detectors
+        self.detector_2d, self.detector_3d = get_detectors(self.configs)
+        self._engine, self._decoder = engine, decoder
         self.current_frame = None
         self.detections_in_current_frame = None
+
+    @property
+    def engine(self):
+        if self._engine is None:
+            from reconstruct.optimizer import _resolve_engine
+            self._engine = _resolve_engine(self._decoder, self.configs)
+        return self._engine
 
     def load_calib(self):
         """Intrinsics of camera 2 and the velodyne -> camera-2 transform, FP32 (`kitti_sequence.py:243-257`):

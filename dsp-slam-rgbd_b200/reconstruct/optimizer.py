@@ -38,7 +38,28 @@ def _engine_for(decoder, device=None, mode="tc"):
     key = (device, mode)
     if key not in per:
         per[key] = Engine(decoder, device=device, mode=mode)
+    global _last_engine
+    _last_engine = weakref.ref(per[key])
     return per[key]
+
+
+_last_engine = None
+
+
+def _resolve_engine(decoder=None, configs=None):
+    """Engine for callers that were not handed a decoder (the sequence classes, constructed by `src/System.cc:99`
+    with `(path, cfg)` only): the decoder's own engine if given; else the engine the process already made for its
+    Optimizer; else one for `get_decoder(configs)` - cached per DeepSDF_DIR, i.e. the very module `System.cc:98`
+    created, so the Optimizer constructed later (`src/LocalMapping.cc:39`) shares it."""
+    if decoder is not None:
+        return _engine_for(decoder)
+    eng = _last_engine() if _last_engine is not None else None
+    if eng is not None and getattr(eng, "_h", None):
+        return eng
+    if configs is None:
+        raise ValueError("no decoder, no configs and no live engine to borrow")
+    from reconstruct.utils import get_decoder
+    return _engine_for(get_decoder(configs))
 
 
 class Optimizer(object):

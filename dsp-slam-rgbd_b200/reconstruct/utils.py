@@ -16,6 +16,7 @@ Mirrored names and what they follow in the reference:
 from __future__ import annotations
 
 import json
+import os
 
 import numpy as np
 
@@ -61,9 +62,17 @@ def get_configs(cfg_file):
     return ForceKeyErrorDict(**cfg_dict)
 
 
+_decoders = {}
+
+
 def get_decoder(configs):
+    """`reconstruct/utils.py:93-94`.  The module is cached per experiment directory: every caller in the process
+    (System.cc:98, the sequence classes, scripts) then holds the SAME nn.Module, hence the same packed engine."""
     from deep_sdf.workspace import config_decoder
-    return config_decoder(configs.DeepSDF_DIR)
+    key = os.path.abspath(configs.DeepSDF_DIR)
+    if key not in _decoders:
+        _decoders[key] = config_decoder(configs.DeepSDF_DIR)
+    return _decoders[key]
 
 
 def create_voxel_grid(vol_dim=128, coord_mode="reference_shear"):
