@@ -18,11 +18,13 @@ every rank optimises its own 16 detections (independent objects, no collective: 
             algorithmic FLOP (3 671 040 per query) / its CUDA-event time measured live inside the timed
             region via dspslam_profile_*; peak = MEASURED_PEAKS.json bf16 dense (sustained figure: the
             kernel is timed inside a long step).
-  cpu_baseline  the numpy oracle port of the reference's algorithm timed on this box's host cores on a
-            bounded sample of the same workload (rank 0, N = 1 only).
+  cpu_baseline  the UNMODIFIED reference optimiser (oracle/_ref: verbatim copy of the reference's hot-path
+            files made by oracle/fetch_ref.py; git-ignored, ships to the box like the .so) timed on this box's
+            host cores on a bounded sample of the same workload (rank 0, N = 1 only); `reference_gpu` is the
+            same unmodified code with its tensors on the B200 (its own .cuda() path, stock PyTorch kernels).
 
-`--impl reference` times the CPU implementation alone (the reference is Python/PyTorch and cannot travel
-to the GPU box; the oracle port restates it, see oracle/dspslam_oracle.py) and prints the same JSON line.
+`--impl reference` times that CPU implementation alone, one C2 detection per step, and prints the same JSON
+line (falls back to the numpy oracle port, kind "port", only if oracle/_ref is absent).
 """
 from __future__ import annotations
 
@@ -109,8 +111,31 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
-# CPU arm: the numpy oracle port of the reference algorithm
+# reference arm: the UNMODIFIED reference optimiser (oracle/_ref, a verbatim copy of the reference's own
+# reconstruct/*.py + deep_sdf/*.py made by oracle/fetch_ref.py) on the host cores, in a child process
+# (oracle/ref_runner.py); the numpy oracle port only where that copy is absent
 # ------------------------------------------------------------------------------------------------
+_CAPS = ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS", "RANK", "WORLD_SIZE", "LOCAL_RANK",
+         "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_RUN_ID")
+
+
+def reference_available():
+    return (os.path.isfile(os.path.join(ROOT, "oracle", "_ref", "reconstruct", "optimizer.py"))
+            or os.path.isfile("/root/reference/reconstruct/optimizer.py"))
+
+
+def run_reference_child(device, n, first=0, warm=1, M=M_PTS, n_bg=N_BG, iters=ITERS, timeout=1500):
+    """Runs oracle/ref_runner.py in a clean child (torchrun caps OMP_NUM_THREADS at 1 for its workers; this process
+    may also hold this repo's own `reconstruct` mirror, which shadows the reference's package name)."""
+    env = {k: v for k, v in os.environ.items() if k not in _CAPS}
+    cmd = [sys.executable, os.path.join(ROOT, "oracle", "ref_runner.py"), "--device", device, "--n", str(n), "--first",
+           str(first), "--M", str(M), "--n-bg", str(n_bg), "--iters", str(iters), "--warm", str(warm)]
+    out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
+    if out.returncode != 0:
+        raise RuntimeError("reference child failed: " + out.stderr[-800:])
+    return json.loads(out.stdout.strip().splitlines()[-1])
+
+
 def cpu_threads():
     try:
         from threadpoolctl import threadpool_info
@@ -120,55 +145,61 @@ def cpu_threads():
         return os.cpu_count() or 1
 
 
-def run_cpu_sample(n_obj, iters):
-    """Times `n_obj` C2-shaped detections for `iters` GN iterations on the host cores; returns (objects/s at the
-    full 10 iterations, seconds spent, threads)."""
+def run_port_sample(n_obj, iters):
+    """Fallback CPU arm (no oracle/_ref): the numpy oracle port; returns seconds per detection, threads."""
     from dspslam import synth
     from oracle import dspslam_oracle as orc
     dec = synth.load_wfit()
     cfg = synth.kitti_config()
     cfg.optimizer.joint_optim.num_iterations = iters
     opt = orc.OracleOptimizer(orc.OracleDecoder(dec.state_dict()), cfg)
-    dets = make_dets(0, n_obj)
-    t0 = time.perf_counter()
-    for d in dets:
+    secs = []
+    for d in make_dets(0, n_obj):
+        t0 = time.perf_counter()
         opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
-    dt = time.perf_counter() - t0
-    per_obj_full = dt / n_obj * (ITERS / iters)
-    return 1.0 / per_obj_full, dt, cpu_threads()
+        secs.append(time.perf_counter() - t0)
+    return secs, cpu_threads()
+
+
+def cpu_sample(n_obj, warm=1):
+    """(seconds per C2 detection [n_obj], threads, kind) on the host cores."""
+    if reference_available():
+        r = run_reference_child("cpu", n_obj, warm=warm)
+        return r["s_per_object"], r["threads"], "reference"
+    if warm:
+        run_port_sample(1, 1)
+    secs, thr = run_port_sample(n_obj, ITERS)
+    return secs, thr, "port"
+
+
+def shared_config(mode="tc", ray_phases=0):
+    """`config` is the same object in both arms (the arms differ in `impl`, not in the workload)."""
+    return {"workload": workload_desc(), "mode": mode, "objects_per_gpu": OBJ_PER_RANK, "ray_phases": ray_phases,
+            "decoder": "DeepSDF 8x512, code 64, W-fit synthetic weights",
+            "l2": "flushed between steps (256 MiB fill, untimed); each step times one dspslam_gn_joint"}
 
 
 def reference_arm(args, rank, world):
+    """One STEP of this arm = ONE detection of the C2 batch (seed = step index) through the unmodified
+    `Optimizer.reconstruct_object` (all 10 GN iterations, torch CPU FP32, every host thread): a bounded sample of
+    the 16-detection batch - the reference itself processes detections one at a time (src/LocalMapping_util.cc:165-206),
+    so objects/s is the same rate.  `ms_per_step` is the time measured per step, `objects_per_step` = 1."""
     if rank != 0:
         return
-    # torchrun exports OMP_NUM_THREADS=1 to its workers; the CPU arm must use all host cores: re-run it in a child
-    # process without the thread caps (and without the rendezvous variables)
-    if world > 1 and not os.environ.get("DSPSLAM_REF_CHILD"):
-        env = {k: v for k, v in os.environ.items()
-               if k not in ("OMP_NUM_THREADS", "MKL_NUM_THREADS", "OPENBLAS_NUM_THREADS", "RANK", "WORLD_SIZE",
-                            "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "ROLE_RANK", "MASTER_ADDR", "MASTER_PORT")}
-        env["DSPSLAM_REF_CHILD"] = "1"
-        sys.stdout.flush()
-        rc = subprocess.call([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--gpus", str(args.gpus),
-                              "--steps", str(args.steps), "--warmup", str(args.warmup)], env=env)
-        if rc != 0:
-            raise SystemExit(rc)
-        return
-    # warm-up (BLAS thread pools, page-in) on a tiny case, then K bounded steps
-    run_cpu_sample(1, 1)
-    vals, secs = [], 0.0
-    for _ in range(max(1, args.steps)):
-        v, dt, thr = run_cpu_sample(1, ITERS)
-        vals.append(v)
-        secs += dt
-    v = float(np.median(vals))
-    sample = ("1 C2 detection x all %d GN iterations per step (%.1f s of CPU work per step), median of %d steps"
-              % (ITERS, secs / len(vals), len(vals)))
+    K = max(1, args.steps)
+    secs, thr, kind = cpu_sample(K, warm=1 if args.warmup > 0 else 0)
+    mean_s = float(np.mean(secs))
+    v = 1.0 / mean_s
+    what = ("the UNMODIFIED reference (oracle/_ref = verbatim reconstruct/optimizer.py:90-205 + loss*.py + deep_sdf, torch CPU FP32)"
+            if kind == "reference" else "numpy oracle port of reconstruct/optimizer.py (oracle/_ref absent)")
+    sample = ("%d steps, each ONE C2 detection (M=%d, N=%d, D=%d) x all %d GN iterations; %.2f s of CPU work per step "
+              "(min %.2f, max %.2f); warm-up = %d C1-sized detection(s), untimed"
+              % (K, M_PTS, M_PTS + N_BG, D_SAMPLES, ITERS, mean_s, min(secs), max(secs), 1 if args.warmup > 0 else 0))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "objects/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * OBJ_PER_RANK / v,
+            "steps": K, "warmup": args.warmup, "ms_per_step": 1e3 * mean_s, "objects_per_step": 1,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_desc(), "impl": "numpy oracle port of reconstruct/optimizer.py on host cores"},
-            "cpu_baseline": {"value": v, "unit": "objects/s", "cores": thr, "kind": "port", "sample": sample},
+            "config": shared_config(), "reference_detail": what,
+            "cpu_baseline": {"value": v, "unit": "objects/s", "cores": thr, "kind": kind, "sample": sample},
             "e2e": {"value": v, "unit": "objects/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -275,10 +306,7 @@ def ours_arm(args, rank, world, local_rank):
         "scaling": "weak", "vs_baseline": None,
         "dtype": "f16 operands, f32 accumulate (tcgen05)" if args.mode == "tc" else "f32",
         "data": "synthetic",
-        "config": {"workload": workload_desc(), "mode": args.mode, "objects_per_gpu": OBJ_PER_RANK,
-                   "ray_phases": args.ray_phases,
-                   "decoder": "DeepSDF 8x512, code 64, W-fit synthetic weights",
-                   "l2": "flushed between steps (256 MiB fill, untimed); each step times one dspslam_gn_joint"},
+        "config": shared_config(args.mode, args.ray_phases),
         "e2e": {"value": total_obj / e2e_s, "unit": "objects/s", "h2d_bytes_per_step": int(batch.h2d_bytes),
                 "d2h_bytes_per_step": int(batch.d2h_bytes)},
         "gpu_launches": int(launches),
@@ -310,11 +338,22 @@ def ours_arm(args, rank, world, local_rank):
         "objects_good": {"resident": n_good, "e2e": e2e_good, "of": OBJ_PER_RANK},
     }
     if world == 1 and not args.no_cpu:
-        run_cpu_sample(1, 1)
-        v, dt, thr = run_cpu_sample(1, ITERS)
-        line["cpu_baseline"] = {"value": v, "unit": "objects/s", "cores": thr, "kind": "port",
-                                "sample": "1 of the %d C2 detections x all %d GN iterations (%.1f s of CPU work)"
-                                          % (OBJ_PER_RANK, ITERS, dt)}
+        secs, thr, kind = cpu_sample(2, warm=1)
+        line["cpu_baseline"] = {"value": 1.0 / float(np.mean(secs)), "unit": "objects/s", "cores": thr, "kind": kind,
+                                "sample": "2 of the %d C2 detections x all %d GN iterations, one at a time as the reference "
+                                          "runs them (%.1f s of CPU work), %s" % (
+                                              OBJ_PER_RANK, ITERS, sum(secs),
+                                              "unmodified reference optimiser (oracle/_ref), torch CPU FP32" if kind == "reference"
+                                              else "numpy oracle port")}
+        if reference_available():
+            # like-for-like GPU figure: the unmodified reference on this B200 through its own .cuda() path
+            try:
+                r = run_reference_child("cuda", 4, warm=2, timeout=600)
+                line["reference_gpu"] = {"value": r["objects_per_s"], "unit": "objects/s", "kind": "reference",
+                                         "sample": "4 C2 detections, one at a time, unmodified reference with every tensor "
+                                                   "on this GPU (stock PyTorch %s FP32 kernels)" % r["torch"]}
+            except Exception as ex:  # noqa: BLE001
+                line["reference_gpu"] = {"unavailable": str(ex)[-300:]}
     else:
         line["cpu_baseline"] = None
     print(json.dumps(line), flush=True)

@@ -48,6 +48,12 @@ struct dspslam_handle {
     std::vector<int> prof_kind;            // kind of each recorded pair
     std::vector<int64_t> prof_rows;        // host-known row count of the pair (stand-alone launches)
     unsigned long long* stats = nullptr;   // device: [0] GN forward rows, [1] GN Jacobian rows
+    // The scratch above (ws, lat, zeros, tc_xtra1, tc_park) is shared by every call on the handle: calls are ordered
+    // on the device by `done` (recorded at the end of every call, waited for by the next call when it arrives on a
+    // different stream), so threads that hand in different CUDA streams cannot race on it.
+    cudaEvent_t done = nullptr;
+    cudaStream_t last_stream = nullptr;
+    bool has_done = false;
 };
 
 namespace {
@@ -61,19 +67,22 @@ struct Carver {   // bump allocator over the workspace (256-byte aligned pieces)
     }
 };
 
-int ensure_ws(dspslam_handle* h, size_t bytes) {
+// Grows the scratch (never shrinks; geometric growth so a sequence of slowly growing batches re-allocates O(log)
+// times).  Stream-ordered: the old block is released and the new one obtained on the calling stream, behind every
+// kernel already queued on it (calls on other streams are ordered in front by StreamOrder) - no device-wide
+// synchronisation on the hot path.
+int ensure_ws(dspslam_handle* h, size_t bytes, cudaStream_t st) {
     if (bytes <= h->ws_cap) return 0;
     if (h->ws) {
-        CK(cudaDeviceSynchronize());
-        CK(cudaFree(h->ws));
+        CK(cudaFreeAsync(h->ws, st));
         h->ws = nullptr;
         h->ws_cap = 0;
     }
-    size_t want = bytes + bytes / 8;
-    cudaError_t e = cudaMalloc(&h->ws, want);
+    size_t want = bytes + bytes / 2;
+    cudaError_t e = cudaMallocAsync(reinterpret_cast<void**>(&h->ws), want, st);
     if (e != cudaSuccess) {
         (void)cudaGetLastError();
-        e = cudaMalloc(&h->ws, bytes);
+        e = cudaMallocAsync(reinterpret_cast<void**>(&h->ws), bytes, st);
         want = bytes;
     }
     if (e != cudaSuccess) {
@@ -176,6 +185,18 @@ void prof_end(dspslam_handle* h, int pair, cudaStream_t st) {
     if (pair >= 0) cudaEventRecord(h->prof_ev[2 * pair + 1], st);
 }
 
+// Orders the calls of one handle on the device across streams (see dspslam_handle::done).
+struct StreamOrder {
+    dspslam_handle* h;
+    cudaStream_t st;
+    StreamOrder(dspslam_handle* h_, void* stream) : h(h_), st(reinterpret_cast<cudaStream_t>(stream)) {
+        if (h->has_done && h->last_stream != st) cudaStreamWaitEvent(st, h->done, 0);
+    }
+    ~StreamOrder() {
+        if (h->done && cudaEventRecord(h->done, st) == cudaSuccess) { h->has_done = true; h->last_stream = st; }
+    }
+};
+
 struct DeviceGuard {
     int prev = -1;
     explicit DeviceGuard(int dev) {
@@ -231,6 +252,8 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     e = cudaMalloc(&h->stats, sizeof(unsigned long long) * 8);
     if (e == cudaSuccess) e = cudaMemset(h->stats, 0, sizeof(unsigned long long) * 8);
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    e = cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming);
+    if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
@@ -246,6 +269,7 @@ void dspslam_destroy(dspslam_handle* h) {
         if (h->wblob) cudaFree(h->wblob);
         if (h->hblob) cudaFree(h->hblob);
         if (h->ws) cudaFree(h->ws);
+        if (h->done) cudaEventDestroy(h->done);
         if (h->lat) cudaFree(h->lat);
         if (h->zeros) cudaFree(h->zeros);
         if (h->stats) cudaFree(h->stats);
@@ -284,6 +308,7 @@ int dspslam_sdf(dspslam_handle* h, void* stream, int mode, const float* code, co
     if (!h) return fail(DSPSLAM_E_BADARG, "null handle");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     return run_sdf(h, stream, mode, code, xyz, n, sdf_out, nullptr);
 }
 
@@ -292,6 +317,7 @@ int dspslam_sdf_jac(dspslam_handle* h, void* stream, int mode, const float* code
     if (!h || !jac_out) return fail(DSPSLAM_E_BADARG, "null handle or jac_out");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     return run_sdf(h, stream, mode, code, xyz, n, sdf_out, jac_out);
 }
 
@@ -300,7 +326,8 @@ int dspslam_mean_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     if (!h || !mean_out || n <= 0) return fail(DSPSLAM_E_BADARG, "bad argument");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    int rc = ensure_ws(h, (size_t)n * sizeof(float));
+    StreamOrder so(h, stream);
+    int rc = ensure_ws(h, (size_t)n * sizeof(float), S(stream));
     if (rc) return rc;
     float* tmp = reinterpret_cast<float*>(h->ws);
     rc = run_sdf(h, stream, mode, code, xyz, n, tmp, nullptr);
@@ -322,6 +349,7 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     float* c0 = h->lat;
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
@@ -342,7 +370,8 @@ int dspslam_marching_cubes(dspslam_handle* h, void* stream, const float* sdf, in
     if ((max_verts > 0 && !verts_out) || (max_tris > 0 && !faces_out)) return fail(DSPSLAM_E_BADARG, "null output");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    int rc = ensure_ws(h, mc_scratch_bytes(G));
+    StreamOrder so(h, stream);
+    int rc = ensure_ws(h, mc_scratch_bytes(G), S(stream));
     if (rc) return rc;
     const int nl = launch_marching_cubes(sdf, G, level, spacing, origin, max_verts, max_tris, verts_out, faces_out,
                                          counts_out, h->ws, S(stream));
@@ -411,7 +440,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
     const size_t o_xtra = c.take(mode != DSPSLAM_MODE_FP32 ? tc_xtra_bytes_per_object() * (size_t)B : 0);
     if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
-    int rc = ensure_ws(h, c.off);
+    int rc = ensure_ws(h, c.off, st);
     if (rc) return rc;
     char* base = h->ws;
     w.st = reinterpret_cast<ObjState*>(base + o_st);
@@ -489,6 +518,7 @@ int dspslam_gn_joint(dspslam_handle* h, void* stream, int mode, const dspslam_jo
     prm.pose_only = 0;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     return gn_run(h, stream, mode, prm, p->num_iterations, p->ray_phases, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
                   total_rays, max_pts, max_rays, t_cam_obj_io, t_cam_obj_io, code_io, code_io, nullptr, status_out,
                   loss_out, dbg_out, DSPSLAM_DBG_STRIDE);
@@ -504,12 +534,13 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
     prm.D = 0;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     // the kernels index ray_off / n_fg even without rays: hand them zero arrays
     if (h->zeros_cap < (size_t)B + 1) {
-        if (h->zeros) { CK(cudaDeviceSynchronize()); CK(cudaFree(h->zeros)); h->zeros = nullptr; h->zeros_cap = 0; }
-        const size_t cap = (size_t)B + 1025;
-        CK(cudaMalloc(&h->zeros, sizeof(int32_t) * cap));
-        CK(cudaMemset(h->zeros, 0, sizeof(int32_t) * cap));
+        if (h->zeros) { CK(cudaFreeAsync(h->zeros, S(stream))); h->zeros = nullptr; h->zeros_cap = 0; }
+        const size_t cap = 2 * (size_t)B + 1025;
+        CK(cudaMallocAsync(reinterpret_cast<void**>(&h->zeros), sizeof(int32_t) * cap, S(stream)));
+        CK(cudaMemsetAsync(h->zeros, 0, sizeof(int32_t) * cap, S(stream)));
         h->zeros_cap = cap;
     }
     return gn_run(h, stream, mode, prm, num_iterations, 1, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
@@ -562,7 +593,8 @@ int dspslam_frame_build_kitti(dspslam_handle* h, void* stream, const dspslam_fra
     }
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    rc = ensure_ws(h, frame_scratch_bytes(n_velo, B, n_masks, d.max_bg));
+    StreamOrder so(h, stream);
+    rc = ensure_ws(h, frame_scratch_bytes(n_velo, B, n_masks, d.max_bg), S(stream));
     if (rc) return rc;
     const int nl = launch_frame_kitti(d, velo, n_velo, bx.data(), front.data(), B, masks, n_masks, bboxes, pts_off,
                                       ray_off, n_fg, pts, rays, depth, info, h->ws, S(stream));
@@ -578,7 +610,8 @@ int dspslam_frame_build_mono(dspslam_handle* h, void* stream, const dspslam_fram
     if (rc) return rc;
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
-    rc = ensure_ws(h, frame_scratch_bytes(0, 1, n_masks, d.max_bg));
+    StreamOrder so(h, stream);
+    rc = ensure_ws(h, frame_scratch_bytes(0, 1, n_masks, d.max_bg), S(stream));
     if (rc) return rc;
     const int nl = launch_frame_mono(d, masks, n_masks, bboxes, rays_out, info_out, h->ws, S(stream));
     return check_launch(h, nl, "dspslam_frame_build_mono");
@@ -589,6 +622,7 @@ int dspslam_pg_from_matrices(dspslam_handle* h, void* stream, const float* T, in
     if (n < 0) return fail(DSPSLAM_E_BADARG, "negative count");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     return check_launch(h, launch_pg_from_matrices(T, n, poses_out, S(stream)), "dspslam_pg_from_matrices");
 }
 
@@ -605,6 +639,7 @@ int dspslam_pg_linearize(dspslam_handle* h, void* stream, const double* vertices
     if (!(inv_sigma > 0.0)) return fail(DSPSLAM_E_BADARG, "inv_sigma must be positive");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     const int nl = launch_pg_linearize(vertices, n_vertices, edge_i, edge_j, measurements, n_edges, inv_sigma,
                                        huber_delta, error, Ji, Jj, chi2, rho, weight, A, b, Hij, S(stream));
     return check_launch(h, nl, "dspslam_pg_linearize");
@@ -615,6 +650,7 @@ int dspslam_pg_oplus(dspslam_handle* h, void* stream, double* vertices, const do
     if (n < 0) return fail(DSPSLAM_E_BADARG, "negative count");
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    StreamOrder so(h, stream);
     return check_launch(h, launch_pg_oplus(vertices, updates, n, S(stream)), "dspslam_pg_oplus");
 }
 

@@ -43,6 +43,7 @@ struct DecoderDev {
     const uint8_t* tc_blob;  // FP16 weight stage images (forward program, then backward program)
     uint8_t* tc_xtra1;       // extras record (layers 0 and 4) of the single-code entry points
     float* tc_park;          // per-CTA scratch of the Jacobian kernels: layer-4 input gradients, [cta][128][68]
+    uint4 tc_layers[2][8];   // per-layer stage table of the forward / backward sweep (kernels_tc.cu: LayerDesc)
 };
 
 // Per-object Gauss-Newton state (one per detection in the batch).

@@ -44,27 +44,7 @@ constexpr int JLD = 76;            // row stride (floats) of the per-row Jacobia
 constexpr int PARK_LD = 68;        // row stride (floats) of the layer-4 input-gradient park in global memory
 constexpr int PARK_CTAS = 256;     // CTAs the park is sized for (grids are capped at the SM count)
 constexpr float GSCALE = 256.f;    // gradients are carried scaled so that FP16 keeps them normal
-constexpr int MAX_PROG = 256;
 constexpr int TMEM_COLS = 512;
-
-enum { ST_FIRST = 1, ST_BEGIN = 2, ST_END = 4, ST_OBJ = 8 };
-
-// One weight stage: what the producer copies and what the MMA thread issues for it.
-struct __align__(16) StageDesc {
-    uint32_t src;      // byte offset in the weight blob (ST_OBJ: inside the object's extras record)
-    uint16_t bytes16;  // bytes / 16
-    uint16_t dcol;     // first accumulator column
-    uint16_t n;        // B rows = accumulator columns covered by the stage
-    uint8_t kind;      // 0: 64B-swizzled K=32 block (2 MMAs of K=16), 1: K=16 extra block (N in chunks of 128)
-    uint8_t kb;        // index of the 32-wide K chunk of the activations (kind 0)
-    uint8_t flags;     // ST_*
-    uint8_t pad[3];
-};
-static_assert(sizeof(StageDesc) == 16, "StageDesc layout");
-
-__constant__ StageDesc c_fwd[MAX_PROG];
-__constant__ StageDesc c_bwd[MAX_PROG];
-__constant__ int c_nprog[2];
 
 // What the producer and the MMA warp walk: one entry per layer of the forward ([0]) and backward ([1])
 // sweep.  The hidden stages of a layer (n in chunks of 256 outputs x k32 chunks of 32 K values, each a
@@ -78,7 +58,9 @@ struct __align__(16) LayerDesc {
     uint32_t pad;
 };
 static_assert(sizeof(LayerDesc) == 16, "LayerDesc layout");
-__constant__ LayerDesc c_layers[2][8];
+static_assert(sizeof(LayerDesc) == sizeof(uint4), "DecoderDev::tc_layers holds LayerDesc entries");
+// The table travels with the decoder view (DecoderDev::tc_layers, kernel parameter space): it belongs to the handle,
+// so two handles holding different decoders on one device cannot overwrite each other's table.
 
 struct TcArgs {
     DecoderDev dec;
@@ -200,7 +182,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             for (int p = 0; p < NPROG; ++p) {
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
-                    const LayerDesc ld = c_layers[p][li];
+                    const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
                     if (ld.xkind) {                              // the K=16 extra block (bias / latent / xyz)
                         mbar_wait(bar_empty(s), ph ^ 1u);
                         if (elect_one()) {
@@ -254,7 +236,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             for (int p = 0; p < NPROG; ++p) {
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
-                    const LayerDesc ld = c_layers[p][li];
+                    const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
                     mbar_wait(bar_aready, aph);                  // this layer's A operand written, accumulator drained
                     aph ^= 1u;
                     if (ld.xkind) {
@@ -698,7 +680,6 @@ std::string g_tc_err;
 
 struct BlobBuilder {
     std::vector<uint8_t> bytes;
-    std::vector<tc::StageDesc> prog[2];
 
     size_t alloc(size_t n) {
         const size_t at = (bytes.size() + 127) & ~(size_t)127;
@@ -740,28 +721,20 @@ size_t tc_xtra_bytes_per_object() { return 2 * (size_t)XTRA_BYTES; }
 int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* const* b, __half** hblob) {
     using namespace tc;
     const int h3 = dec.h3, h3p = dec.h3p, in_dim = dec.in_dim;
-    if (h3p % 64 != 0) {          // the K blocks are 64 wide; code_len 64 gives 448
-        g_tc_err = "tcgen05 path needs (512 - code_len - 3) rounded up to 16 to be a multiple of 64 (code_len 64)";
+    if (h3p % 32 != 0) {          // weight stages are 32 K values wide: code_len 64 gives 448, code_len 32 gives 480
+        g_tc_err = "tcgen05 path needs (512 - code_len - 3) rounded up to 16 to be a multiple of 32 (code_len 64, 32, ...)";
         return 1;
     }
     BlobBuilder B;
-    auto push = [&](int p, size_t src, size_t bytes, int dcol, int n, int kind, int kb, int flags) {
-        StageDesc d{};
-        d.src = (uint32_t)src; d.bytes16 = (uint16_t)(bytes / 16); d.dcol = (uint16_t)dcol; d.n = (uint16_t)n;
-        d.kind = (uint8_t)kind; d.kb = (uint8_t)kb; d.flags = (uint8_t)flags;
-        B.prog[p].push_back(d);
-    };
     LayerDesc layers[2][8];
     memset(layers, 0, sizeof(layers));
-    // ---- forward program ----
-    push(0, 0, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_END | ST_OBJ);            // layer 0: extras only
+    // ---- forward program ----            // layer 0: extras only
     layers[0][0].n = HID; layers[0][0].k32 = 0; layers[0][0].xkind = 2; layers[0][0].xsrc = 0;
     for (int l = 1; l < 8; ++l) {
         const int N = (l == 3) ? h3p : HID, K = (l == 4) ? h3p : HID;
         const int Nreal = (l == 3) ? h3 : HID, Kreal = (l == 4) ? h3 : HID;
         layers[0][l].n = (uint16_t)N; layers[0][l].k32 = (uint8_t)(K / 32);
         if (l == 4) {
-            push(0, XTRA_BYTES, XTRA_BYTES, 0, HID, 1, 0, ST_FIRST | ST_BEGIN | ST_OBJ);
             layers[0][l].xkind = 2; layers[0][l].xsrc = XTRA_BYTES;
         } else {                                                                           // static bias block
             const size_t at = B.alloc((size_t)N * 32);
@@ -772,7 +745,6 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
                 memcpy(&B.bytes[off], &hi, 2);
                 memcpy(&B.bytes[off + 2], &lo, 2);
             }
-            push(0, at, (size_t)N * 32, 0, N, 1, 0, ST_FIRST | ST_BEGIN);
             layers[0][l].xkind = 1; layers[0][l].xsrc = (uint32_t)at;
         }
         const float* Wl = W[l];
@@ -782,9 +754,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
                 const size_t at = B.sw64(n0, nn, kb, [&](int n, int k) -> float {
                     return (n < Nreal && k < Kreal) ? Wl[(size_t)n * HID + k] : 0.f;        // W[l] is [out][512]
                 });
-                const bool end = (n0 + nn == N) && (kb == K / 32 - 1);
                 if (n0 == 0 && kb == 0) layers[0][l].src = (uint32_t)at;
-                push(0, at, (size_t)nn * 64, n0, nn, 0, kb, end ? ST_END : 0);
             }
         }
     }
@@ -798,12 +768,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
                 const size_t at = B.sw64(n0, 256, kb, [&](int i, int o) -> float {
                     return (o < Kreal) ? Wl[(size_t)o * HID + i] : 0.f;
                 });
-                int fl = 0;
-                if (kb == 0) fl |= ST_FIRST;
-                if (n0 == 0 && kb == 0) fl |= ST_BEGIN;
-                if (n0 == HID - 256 && kb == K / 32 - 1) fl |= ST_END;
                 if (n0 == 0 && kb == 0) layers[1][7 - l].src = (uint32_t)at;
-                push(1, at, 256 * 64, n0, 256, 0, kb, fl);
             }
         }
     }
@@ -814,14 +779,9 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
             const size_t at = B.sw64(0, N0, kb, [&](int i, int o) -> float {
                 return (i < in_dim) ? W[0][(size_t)o * in_dim + i] : 0.f;
             });
-            int fl = 0;
-            if (kb == 0) fl |= ST_FIRST | ST_BEGIN;
-            if (kb == HID / 32 - 1) fl |= ST_END;
             if (kb == 0) layers[1][7].src = (uint32_t)at;
-            push(1, at, (size_t)N0 * 64, 0, N0, 0, kb, fl);
         }
     }
-    if (B.prog[0].size() > MAX_PROG || B.prog[1].size() > MAX_PROG) { g_tc_err = "stage program too long"; return 2; }
 
     // device: [weight images | one extras record for the single-code entry points]
     const size_t wbytes = (B.bytes.size() + 255) & ~(size_t)255;
@@ -832,11 +792,6 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     if (e != cudaSuccess) { g_tc_err = cudaGetErrorString(e); return 2; }
     e = cudaMemcpy(dev, B.bytes.data(), B.bytes.size(), cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemset(dev + wbytes, 0, 2 * XTRA_BYTES);
-    const int np[2] = {(int)B.prog[0].size(), (int)B.prog[1].size()};
-    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_fwd, B.prog[0].data(), sizeof(StageDesc) * np[0]);
-    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_bwd, B.prog[1].data(), sizeof(StageDesc) * np[1]);
-    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_nprog, np, sizeof(np));
-    if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_layers, layers, sizeof(layers));
 #define TC_ATTR(MODE)                                                                                          \
     if (e == cudaSuccess)                                                                                      \
         e = cudaFuncSetAttribute(k_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<MODE>::SMEM);
@@ -851,6 +806,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     dec.tc_blob = dev;
     dec.tc_xtra1 = dev + wbytes;
     dec.tc_park = reinterpret_cast<float*>(dev + wbytes + 2 * XTRA_BYTES);
+    memcpy(dec.tc_layers, layers, sizeof(layers));
     return 0;
 }
 

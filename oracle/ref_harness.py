@@ -1,6 +1,7 @@
-"""Import the UNMODIFIED reference (`/root/reference`) in the build container.
-TEST INFRASTRUCTURE - used only by `oracle/make_goldens.py` (golden-vector
-generation) here; `/root/reference` does not exist on the GPU box.
+"""Import the UNMODIFIED reference: `/root/reference` in the build container, else the verbatim copy of its
+hot-path files under `oracle/_ref/` (made by `oracle/fetch_ref.py`, git-ignored, travels to the GPU box).
+TEST INFRASTRUCTURE - used by `oracle/make_goldens*.py` (golden-vector generation), `oracle/ref_runner.py`
+(the timed reference arm of bench.py) and tests; never by the product.
 
 Shims (harness side only, reference files untouched - SURVEY.md Appendix B):
   * stub modules for `addict`, `plyfile`, `skimage.measure` (absent here);
@@ -8,10 +9,16 @@ Shims (harness side only, reference files untouched - SURVEY.md Appendix B):
 """
 from __future__ import annotations
 
+import os
 import sys
 import types
 
-REF_ROOT = "/root/reference"
+_LOCAL = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+REF_ROOT = os.environ.get("DSPSLAM_REF_ROOT") or ("/root/reference" if os.path.isdir("/root/reference/reconstruct") else _LOCAL)
+
+
+def available():
+    return os.path.isfile(os.path.join(REF_ROOT, "reconstruct", "optimizer.py"))
 
 
 class _Dict(dict):
@@ -44,9 +51,11 @@ class _Dict(dict):
         self[k] = v
 
 
-def import_reference():
+def import_reference(force_cpu=False):
     """Returns the reference's modules as a namespace; must run in a process
-    that has NOT imported this repo's own `reconstruct` / `deep_sdf` mirrors."""
+    that has NOT imported this repo's own `reconstruct` / `deep_sdf` mirrors.
+    force_cpu: make the reference's unconditional `.cuda()` calls no-ops even on a host with a GPU
+    (the CPU-timed arm); otherwise they are left alone where CUDA is available."""
     import torch
     for name in ("reconstruct", "deep_sdf"):
         if name in sys.modules and REF_ROOT not in getattr(sys.modules[name], "__file__", ""):
@@ -60,7 +69,7 @@ def import_reference():
     sk.measure = skm
     sys.modules.setdefault("skimage", sk)
     sys.modules.setdefault("skimage.measure", skm)
-    if not torch.cuda.is_available():
+    if force_cpu or not torch.cuda.is_available():
         torch.Tensor.cuda = lambda self, *a, **k: self
         torch.nn.Module.cuda = lambda self, *a, **k: self
         torch.cuda.synchronize = lambda *a, **k: None
