@@ -128,6 +128,9 @@ def run_reference_child(device, n, first=0, warm=1, M=M_PTS, n_bg=N_BG, iters=IT
     """Runs oracle/ref_runner.py in a clean child (torchrun caps OMP_NUM_THREADS at 1 for its workers; this process
     may also hold this repo's own `reconstruct` mirror, which shadows the reference's package name)."""
     env = {k: v for k, v in os.environ.items() if k not in _CAPS}
+    if device == "cpu":
+        env["CUDA_VISIBLE_DEVICES"] = ""     # the CPU arm must not see the GPU (DataParallel in the reference's
+                                             # config_decoder moves the module to cuda:0 whenever one is visible)
     cmd = [sys.executable, os.path.join(ROOT, "oracle", "ref_runner.py"), "--device", device, "--n", str(n), "--first",
            str(first), "--M", str(M), "--n-bg", str(n_bg), "--iters", str(iters), "--warm", str(warm)]
     out = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=timeout)
@@ -296,6 +299,8 @@ def ours_arm(args, rank, world, local_rank):
     rows_fwd_all = sum_over_ranks(prof["rows_gn_fwd"])
     rows_jac_all = sum_over_ranks(prof["rows_gn_jac"])
 
+    extra = other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ranks, sum_over_ranks)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -336,7 +341,12 @@ def ours_arm(args, rank, world, local_rank):
                          "forward_kernel_only": prof["rows_gn_fwd"] / max(1e-9, prof["ms_gn_fwd"] * 1e-3) / 1e6,
                          "sdf_jacobian_kernel_only": prof["rows_gn_jac"] / max(1e-9, prof["ms_gn_jac"] * 1e-3) / 1e6},
         "objects_good": {"resident": n_good, "e2e": e2e_good, "of": OBJ_PER_RANK},
+        "refine": {"rows": int(prof["rows_gn_refine"]), "launches": int(prof["n_gn_refine"]), "ms": prof["ms_gn_refine"],
+                   "share_of_step": prof["ms_gn_refine"] / max(1e-9, float(np.sum(step_ms))),
+                   "note": "ray samples within refine_window * cut_off of a decision threshold, evaluated a second "
+                           "time with hi+lo FP16 operand pairs (k_tc_refine) before the per-ray scan"},
     }
+    line.update(extra)
     if world == 1 and not args.no_cpu:
         secs, thr, kind = cpu_sample(2, warm=1)
         line["cpu_baseline"] = {"value": 1.0 / float(np.mean(secs)), "unit": "objects/s", "cores": thr, "kind": kind,
@@ -361,6 +371,96 @@ def ours_arm(args, rank, world, local_rank):
         dist.destroy_process_group()
 
 
+def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ranks, sum_over_ranks):
+    """The other BASELINE.json configs under the driver's clock, a few repetitions each (rank 0 returns the keys):
+      c1  single KITTI-style car through `reconstruct_object` with host arrays (latency; rank 0 only)
+      c4  256^3 mesh grid, slabs over the ranks + overlapped NCCL all-gathers (the one collective of the design)
+      c5  1 024 C1-shaped detections split contiguously over the ranks, H2D / D2H included
+      parity  statistics of this mode against the reference-made vectors in tests/golden (tools/parity_stats.py)"""
+    import torch
+    import torch.distributed as dist
+    from dspslam import synth
+    from dspslam.dist import grid_sdf_sharded, shard_range
+    out = {}
+    if args.skip_configs:
+        return out
+    eng = opt.engine
+    # ---- C1 latency ----
+    if rank == 0:
+        d = synth.make_kitti_detection(0)
+        for _ in range(3):
+            o = opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        reps = 20
+        for _ in range(reps):
+            o = opt.reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"])
+        torch.cuda.synchronize()
+        out["c1"] = {"workload": "C1 single KITTI-style car: 250 surface pts + 450 rays x 50 samples, 10 GN iters, "
+                                 "reconstruct_object() from host arrays",
+                     "c1_ms_per_object": 1e3 * (time.perf_counter() - t0) / reps, "is_good": bool(o.is_good)}
+    barrier()
+    # ---- C4 grid + all-gather ----
+    G = 256
+    code = np.zeros(64, np.float32)
+    code[:3] = [0.2, -0.1, 0.3]
+    grid_sdf_sharded(eng, code, G, mode=args.mode)
+    barrier()
+    tm, tot, comp, expo = {}, [], [], []
+    for _ in range(3):
+        barrier()
+        vol = grid_sdf_sharded(eng, code, G, mode=args.mode, timing=tm)
+        tot.append(tm["ms_total"]); comp.append(tm["ms_compute"]); expo.append(tm["ms_allgather_exposed"])
+    ms_tot = max_over_ranks(float(np.median(tot)))
+    ms_comp = max_over_ranks(float(np.median(comp)))
+    ms_expo = max_over_ranks(float(np.median(expo)))
+    ms_ag = 0.0
+    if world > 1:                                   # the all-gather of the whole volume alone (no compute to hide behind)
+        buf = torch.empty(((G ** 3 + world - 1) // world) * world, dtype=torch.float32, device=eng.device)
+        per = buf.numel() // world
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+        dist.all_gather_into_tensor(buf, buf[rank * per:(rank + 1) * per].clone())
+        barrier()
+        ev[0].record()
+        for _ in range(3):
+            dist.all_gather_into_tensor(buf, buf[rank * per:(rank + 1) * per])
+        ev[1].record()
+        torch.cuda.synchronize()
+        ms_ag = max_over_ranks(ev[0].elapsed_time(ev[1]) / 3)
+    checksum = float(vol.double().sum().item())
+    out["c4"] = {"workload": "C4 mesh grid 256^3 (16.8 M queries): slabs over the ranks, one NCCL all-gather per piece "
+                             "overlapping the next piece's kernel",
+                 "ms_grid": ms_tot, "ms_slab_compute": ms_comp, "ms_allgather_exposed": ms_expo,
+                 "ms_allgather_alone": ms_ag, "ms_allgather_hidden": max(0.0, ms_ag - ms_expo), "pieces": tm.get("pieces"),
+                 "mquery_per_s": G ** 3 / ms_tot / 1e3, "tflops": G ** 3 * FLOP_FWD / ms_tot / 1e9, "checksum": checksum}
+    del vol
+    # ---- C5 sweep ----
+    n_total = 1024
+    lo, hi = shard_range(n_total, rank, world)
+    dets = [synth.make_kitti_detection(k) for k in range(lo, hi)]
+    opt5 = opt
+    opt5.reconstruct_objects(dets[:64])
+    barrier()
+    t0 = time.perf_counter()
+    outs = opt5.reconstruct_objects(dets)
+    torch.cuda.synchronize()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    good = int(sum_over_ranks(float(sum(1 for o in outs if o.is_good))))
+    out["c5"] = {"workload": "C5 throughput sweep: 1024 C1-shaped detections split contiguously over the ranks, "
+                             "H2D / D2H included, one pass", "seconds": dt, "objects_per_s": n_total / dt, "good": good}
+    barrier()
+    # ---- parity of the benchmarked mode against the reference's vectors ----
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import parity_stats
+        try:
+            out["parity"] = parity_stats.parity(eng, args.mode)
+        except Exception as ex:  # noqa: BLE001
+            out["parity"] = {"error": str(ex)[-300:]}
+    barrier()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -369,6 +469,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--mode", default="tc", choices=["tc", "fp32"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--skip-configs", action="store_true", help="skip the c1 / c4 / c5 / parity legs")
     ap.add_argument("--ray-phases", type=int, default=0,
                     help="render term: 1 = evaluate every in-ball sample like the reference, 2..4 = early ray "
                          "termination in that many phases (bit-identical results), 0 = library default")

@@ -41,6 +41,7 @@ struct dspslam_handle {
     size_t zeros_cap = 0;
     int64_t launches = 0;
     bool tc_ready = false;
+    std::string tc_why;          // why the tcgen05 path is unavailable for this decoder
     std::mutex mu;
     // profiling (dspslam_profile_*): event pairs around decoder launches + device row counters
     bool prof_on = false;
@@ -165,7 +166,7 @@ int check_launch(dspslam_handle* h, int n_launch, const char* what) {
     return 0;
 }
 
-enum { PK_GN_FWD = 0, PK_GN_JAC = 1, PK_ROWS_FWD = 2, PK_ROWS_JAC = 3 };
+enum { PK_GN_FWD = 0, PK_GN_JAC = 1, PK_ROWS_FWD = 2, PK_ROWS_JAC = 3, PK_GN_REFINE = 4 };
 
 // records the start event of a profiled launch group; returns the pair index or -1
 int prof_begin(dspslam_handle* h, int kind, int64_t rows, cudaStream_t st) {
@@ -214,6 +215,13 @@ extern "C" {
 int dspslam_abi_version(void) { return DSPSLAM_ABI_VERSION; }
 const char* dspslam_last_error(void) { return g_err.c_str(); }
 int64_t dspslam_launch_count(const dspslam_handle* h) { return h ? h->launches : 0; }
+int dspslam_mode_available(const dspslam_handle* h, int mode) {
+    if (!h) { g_err = "null handle"; return 0; }
+    if (mode == DSPSLAM_MODE_FP32) return 1;
+    if (mode != DSPSLAM_MODE_TC) { g_err = "unknown mode"; return 0; }
+    if (!h->tc_ready) { g_err = h->tc_why; return 0; }
+    return 1;
+}
 
 int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host, const float* const* b_host,
                    int device, dspslam_handle** out) {
@@ -257,6 +265,7 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
+    if (rc == 1) h->tc_why = tc_last_error();
     *out = h;
     return 0;
 }
@@ -285,7 +294,7 @@ static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
     if (n == 0) return 0;                       // empty query: nothing to do (pointers may be null)
     if (!code || !xyz || !sdf_out) return fail(DSPSLAM_E_BADARG, "null argument");
     if (n > ((int64_t)1 << 31) - 256) return fail(DSPSLAM_E_BADARG, "n too large for one call");
-    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     float* c0 = h->lat;
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
@@ -346,7 +355,7 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
         return fail(DSPSLAM_E_BADARG, "bad coord_mode");
     if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
     if (i1 == i0) return 0;
-    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     StreamOrder so(h, stream);
@@ -378,14 +387,15 @@ int dspslam_marching_cubes(dspslam_handle* h, void* stream, const float* sdf, in
     return check_launch(h, nl, "dspslam_marching_cubes");
 }
 
-static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int ray_phases, int B,
+static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDev& prm, int iters, int ray_phases,
+                  float refine_window, int B,
                   const int32_t* pts_off, const int32_t* ray_off, const int32_t* n_fg, const float* pts,
                   const float* rays, const float* depth, int64_t total_pts, int64_t total_rays, int max_pts,
                   int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
                   const float* scale_in, int32_t* status_out, float* loss_out, float* dbg_out, int dbg_stride) {
     // diagnostic mixes (not in the public header): 2 = tensor-core forward samples + FP32 Jacobian rows, 3 = the reverse
     if (mode < 0 || mode > 3) return fail(DSPSLAM_E_BADARG, "bad mode");
-    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable");
+    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2), jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3);
     if (B <= 0 || B > 65535) return fail(DSPSLAM_E_BADARG, "B must be in 1..65535");
     if (iters < 0) return fail(DSPSLAM_E_BADARG, "negative iteration count");
@@ -413,7 +423,12 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.n_phases = ray_phases ? ray_phases : ((V / GROUP_ROWS >= (int64_t)h->sm_count * 8) ? 2 : 1);
     w.phase = 0;
 
-    const size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
+    // second, FP32-grade evaluation of the ray samples next to a decision threshold (tensor-core forward pass only)
+    const bool refine = fwd_tc && !prm.pose_only && refine_window >= 0.f;
+    w.refine_eps = refine ? (refine_window > 0.f ? refine_window : 0.1f) * prm.th : 0.f;
+    const size_t rgroups_max = refine ? (size_t)(((int64_t)max_rays * D + REFINE_ROWS - 1) / REFINE_ROWS) : 0;
+    size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
+    if ((size_t)B * rgroups_max + 1 > max_tiles) max_tiles = (size_t)B * rgroups_max + 1;
     Carver c;
     const size_t o_st = c.take(sizeof(ObjState) * B);
     const size_t o_code = c.take(sizeof(float) * MAX_L * B);
@@ -421,6 +436,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_c4 = c.take(sizeof(float) * HID * B);
     const size_t o_frows = c.take(sizeof(float4) * (size_t)V);
     const size_t o_sdf = c.take(sizeof(float) * (size_t)V);
+    const size_t o_rrows = c.take(refine ? sizeof(float4) * (size_t)V : 0);
     const size_t o_rcnt = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_roff = c.take(sizeof(int) * (size_t)total_rays);
     const size_t o_rhit = c.take(sizeof(int) * (size_t)total_rays);
@@ -449,6 +465,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.c4 = reinterpret_cast<float*>(base + o_c4);
     w.frows = reinterpret_cast<float4*>(base + o_frows);
     w.sdf_samp = reinterpret_cast<float*>(base + o_sdf);
+    w.rrows = reinterpret_cast<float4*>(base + o_rrows);
     w.ray_cnt = reinterpret_cast<int*>(base + o_rcnt);
     w.ray_roff = reinterpret_cast<int*>(base + o_roff);
     w.ray_hit = reinterpret_cast<int*>(base + o_rhit);
@@ -490,6 +507,12 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                 prof_end(h, pf, st);
             }
             w.phase = 0;
+            if (refine) {
+                launch_gn_refine_plan(w, st); ++nl;
+                const int pr = prof_begin(h, PK_GN_REFINE, 0, st);
+                nl += tc_launch_gn_refine(w, h->sm_count, st);
+                prof_end(h, pr, st);
+            }
             launch_gn_rays(w, max_rays, st); nl += 2;
         }
         const int pj = prof_begin(h, PK_GN_JAC, 0, st);
@@ -519,7 +542,7 @@ int dspslam_gn_joint(dspslam_handle* h, void* stream, int mode, const dspslam_jo
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     StreamOrder so(h, stream);
-    return gn_run(h, stream, mode, prm, p->num_iterations, p->ray_phases, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
+    return gn_run(h, stream, mode, prm, p->num_iterations, p->ray_phases, p->refine_window, B, pts_off, ray_off, n_fg, pts, rays, depth, total_pts,
                   total_rays, max_pts, max_rays, t_cam_obj_io, t_cam_obj_io, code_io, code_io, nullptr, status_out,
                   loss_out, dbg_out, DSPSLAM_DBG_STRIDE);
 }
@@ -543,7 +566,7 @@ int dspslam_gn_pose_only(dspslam_handle* h, void* stream, int mode, int num_iter
         CK(cudaMemsetAsync(h->zeros, 0, sizeof(int32_t) * cap, S(stream)));
         h->zeros_cap = cap;
     }
-    return gn_run(h, stream, mode, prm, num_iterations, 1, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
+    return gn_run(h, stream, mode, prm, num_iterations, 1, -1.f, B, pts_off, h->zeros, h->zeros, pts, nullptr, nullptr,
                   total_pts, 0, max_pts, 0, t_co_se3_io, t_co_se3_io, code, nullptr, scale, nullptr, nullptr, dbg_out,
                   64);
 }
@@ -671,8 +694,8 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     memset(out, 0, sizeof(*out));
-    double ms[4] = {0, 0, 0, 0};
-    int64_t rows[4] = {0, 0, 0, 0}, cnt[4] = {0, 0, 0, 0};
+    double ms[5] = {0, 0, 0, 0, 0};
+    int64_t rows[5] = {0, 0, 0, 0, 0}, cnt[5] = {0, 0, 0, 0, 0};
     for (size_t p = 0; p < h->prof_kind.size(); ++p) {
         CK(cudaEventSynchronize(h->prof_ev[2 * p + 1]));
         float t = 0.f;
@@ -694,6 +717,7 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
     out->rows_fwd = rows[PK_ROWS_FWD]; out->rows_jac = rows[PK_ROWS_JAC];
     out->n_gn_fwd = cnt[PK_GN_FWD]; out->n_gn_jac = cnt[PK_GN_JAC];
     out->n_rows_fwd = cnt[PK_ROWS_FWD]; out->n_rows_jac = cnt[PK_ROWS_JAC];
+    out->rows_gn_refine = (int64_t)st[3]; out->n_gn_refine = cnt[PK_GN_REFINE]; out->ms_gn_refine = ms[PK_GN_REFINE];
     return 0;
 }
 

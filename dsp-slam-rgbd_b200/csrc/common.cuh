@@ -15,6 +15,7 @@ constexpr int HMAX = POSE + MAX_L;   // 71
 constexpr int GROUP_ROWS = 128;      // rows per work unit (one partial-H slot, one tcgen05 M tile)
 constexpr int PART_STRIDE = 5120;    // floats per partial slot: H (<=71x71) | b (<=71) | 2 loss sums
 constexpr int PART_LOSS = 5112;      // [5112] sum rt^2 surface rows, [5113] sum rt^2 render rows
+constexpr int REFINE_ROWS = 64;      // real rows per tile of the refinement kernel (hi rows | lo rows stacked to M = 128)
 constexpr int MAX_PHASES = 4;        // front-to-back passes over the ray samples per iteration (k_gn_sample)
 constexpr float SDF_OUTSIDE = 1e30f; // sentinel SDF of ray samples outside the unit ball (occupancy 0)
 
@@ -58,7 +59,7 @@ struct ObjState {
     int K;            // render rows this iteration
     int M_active;     // surface rows in use (pose-only inlier cut)
     float sdf_loss, render_loss, loss;
-    float pad1;
+    int rf_rows;      // ray samples of this iteration queued for the FP32-grade second evaluation (kernels_tc.cu: k_tc_refine)
     int ph_rows[MAX_PHASES];   // in-ball samples handed to the decoder in each ray phase of this iteration
 };
 

@@ -38,13 +38,15 @@ __device__ __forceinline__ void pack_extra_row(const DecoderDev& dec, int which,
     *reinterpret_cast<uint4*>(dst + 128) = *reinterpret_cast<const uint4*>(&h[8]);
 }
 
-// rows object b contributes to work list `which` (0: ray samples of the current phase, 1: Jacobian rows)
+// rows object b contributes to work list `which` (0: ray samples of the current phase, 1: Jacobian rows,
+// 2: ray samples queued for the second, FP32-grade evaluation - tiles of REFINE_ROWS rows)
 // (volatile: the fields were written by other CTAs of the running kernel; an L1 line cached earlier by this CTA
 // could be stale)
 __device__ __forceinline__ int plan_rows(const GnWork& w, int which, int b) {
     const volatile ObjState* st = w.st + b;
     if (st->status != 0) return 0;
     if (which == 0) return st->ph_rows[w.phase];
+    if (which == 2) return st->rf_rows;
     return (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : st->K);
 }
 
@@ -57,11 +59,12 @@ static __device__ void plan_tiles(const GnWork& w, int which) {
     __shared__ int s_carry;
     __shared__ int s_off[1025];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
+    const int TR = (which == 2) ? REFINE_ROWS : GROUP_ROWS;      // rows per tile
     if (tid == 0) s_carry = 0;
     __syncthreads();
     for (int base = 0; base < w.B; base += blockDim.x) {
         const int b = base + tid;
-        const int nt = (b < w.B) ? (plan_rows(w, which, b) + GROUP_ROWS - 1) / GROUP_ROWS : 0;
+        const int nt = (b < w.B) ? (plan_rows(w, which, b) + TR - 1) / TR : 0;
         int inc = nt;
         for (int o = 1; o < 32; o <<= 1) {
             const int t = __shfl_up_sync(0xffffffffu, inc, o);
@@ -100,7 +103,7 @@ static __device__ void plan_tiles(const GnWork& w, int which) {
     for (int t = tid; t < total; t += blockDim.x) {
         const int b = find_segment(off, w.B, t);
         w.tile_obj[t] = b;
-        w.tile_row0[t] = (t - off[b]) * GROUP_ROWS;
+        w.tile_row0[t] = (t - off[b]) * TR;
     }
 }
 

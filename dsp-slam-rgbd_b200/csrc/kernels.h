@@ -30,6 +30,9 @@ struct GnWork {
     float4* frows;        // [total_rays*D]  compacted in-ball samples per object: x,y,z,dest; after the forward
                           //                 phases: staging of the selected render rows, ray r at [r*D, r*D+cnt)
     float* sdf_samp;      // [total_rays*D]  SDF per ray sample (SDF_OUTSIDE outside the ball)
+    float4* rrows;        // [total_rays*D]  per object: samples the FP16 forward pass left within refine_eps of a decision
+                          //                 threshold (| |s| - th | < eps): x,y,z,dest; re-evaluated by k_tc_refine
+    float refine_eps;     // 0: no second evaluation (FP32 mode, or switched off)
     int* ray_cnt;         // [total_rays]
     int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its 128-ray chunk
     int* chunk_cnt;       // [B][ray_chunks] rows selected by each chunk of rays, then (scanned) the chunk's first row
@@ -44,7 +47,7 @@ struct GnWork {
     // tcgen05 path work lists (filled by k_gn_plan_*)
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object
-    int* n_tiles;         // [2] number of forward / Jacobian tiles
+    int* n_tiles;         // [3] number of forward / Jacobian / refinement tiles
     int* tile_off;        // [B+1] first tile of each object in the list being planned (scratch of plan_tiles)
     unsigned int* done;   // [2] "last CTA done" tickets of k_gn_sample / k_gn_ray_count (zero between launches)
     unsigned int* done_obj; // [B] per-object tickets of k_gn_ray_count
@@ -72,6 +75,7 @@ void launch_gn_final(const GnWork& w, float* pose_out, float* code_out, int code
                      int* status_out, float* loss_out, cudaStream_t st);
 void launch_gn_sample(const GnWork& w, cudaStream_t st);
 void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st);
+void launch_gn_refine_plan(const GnWork& w, cudaStream_t st);
 void launch_gn_rays(const GnWork& w, int max_rays, cudaStream_t st);
 void launch_gn_jac_simt(const GnWork& w, cudaStream_t st);
 void launch_gn_solve(const GnWork& w, int iter, int last_iter, float* dbg, int dbg_stride, cudaStream_t st);

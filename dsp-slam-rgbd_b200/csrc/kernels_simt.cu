@@ -122,7 +122,7 @@ __global__ void k_gn_init(GnWork w, const float* __restrict__ pose_in, const flo
                 for (int j = 0; j < 3; ++j) T[i * 4 + j] *= sc;
         }
         inv_affine(T, s.T_oc);
-        s.status = 0; s.n_valid = 0; s.K = 0; s.M_active = M;
+        s.status = 0; s.n_valid = 0; s.K = 0; s.M_active = M; s.rf_rows = 0;
         for (int p = 0; p < MAX_PHASES; ++p) s.ph_rows[p] = 0;
         s.sdf_loss = 0.f; s.render_loss = 0.f; s.loss = 0.f;
     }
@@ -153,6 +153,7 @@ __device__ void prep_object(const GnWork& w, int b, int iter) {
         s.rot_res = w.prm.pose_only ? 0.f : rot_prior(s.T_co, sc, s.rotJ);
         s.n_valid = 0;
         for (int p = 0; p < MAX_PHASES; ++p) s.ph_rows[p] = 0;
+        s.rf_rows = 0;
         s.K = 0;
         cnt = 0;
     }
@@ -301,7 +302,8 @@ __global__ void __launch_bounds__(256) k_gn_sample(GnWork w) {
             for (int h = 0; h < 2; ++h) {
                 const int j = h * 32 + lane;
                 if (j >= j_lo && j < start && ((mask >> j) & 1ull))
-                    hit |= w.sdf_samp[(size_t)warp * D + j] <= -w.prm.th;
+                    hit |= w.sdf_samp[(size_t)warp * D + j] <= -(w.prm.th + w.refine_eps);   // surely closed: a sample inside
+                                                                   // the refinement window may still open up again
             }
             if (__any_sync(0xffffffffu, hit)) end = start;
         }
@@ -348,6 +350,16 @@ __global__ void __launch_bounds__(256) k_gn_sample(GnWork w) {
         }
     }
     if (w.tc && last_cta_done(w.done + 0)) plan_tiles(w, 0);
+}
+
+// tile list of the refinement kernel (one CTA; runs behind the last forward phase, whose epilogues queued the rows)
+__global__ void __launch_bounds__(256) k_gn_refine_plan(GnWork w) {
+    plan_tiles(w, 2);
+    if (w.stats && threadIdx.x == 0) {
+        unsigned long long n = 0;
+        for (int b = 0; b < w.B; ++b) n += (unsigned long long)w.st[b].rf_rows;
+        atomicAdd(w.stats + 3, n);
+    }
 }
 
 // forward-only SDF of the compacted in-ball samples, FP32 path (grid: groups x objects)
@@ -882,6 +894,7 @@ void launch_gn_sample(const GnWork& w, cudaStream_t st) {
     const int64_t threads = (int64_t)w.total_rays * 32;       // (no rays: one CTA that only plans an empty tile list)
     k_gn_sample<<<(unsigned)((threads + 255) / 256 > 0 ? (threads + 255) / 256 : 1), 256, 0, st>>>(w);
 }
+void launch_gn_refine_plan(const GnWork& w, cudaStream_t st) { k_gn_refine_plan<<<1, 256, 0, st>>>(w); }
 void launch_gn_fwd_simt(const GnWork& w, cudaStream_t st) {
     if (w.fgroups_max == 0) return;
     k_gn_fwd_simt<<<dim3(w.fgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);

@@ -15,10 +15,10 @@ MODE_FP32, MODE_TC = 0, 1
 ST_OK, ST_FEW_POINTS, ST_NAN = 0, 1, 2
 GRID_REFERENCE_SHEAR, GRID_LATTICE = 0, 1
 DBG_STRIDE = 5120
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 EXPORTS = [
-    "dspslam_abi_version", "dspslam_last_error", "dspslam_launch_count", "dspslam_create",
+    "dspslam_abi_version", "dspslam_last_error", "dspslam_launch_count", "dspslam_mode_available", "dspslam_create",
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
     "dspslam_marching_cubes", "dspslam_frame_build_kitti", "dspslam_frame_build_mono",
@@ -38,13 +38,14 @@ class JointParams(C.Structure):
     _fields_ = [("k1", C.c_float), ("k2", C.c_float), ("k3", C.c_float), ("k4", C.c_float),
                 ("b1", C.c_float), ("b2", C.c_float), ("lr", C.c_float), ("s_damp", C.c_float),
                 ("cut_off", C.c_float), ("num_iterations", C.c_int32),
-                ("num_depth_samples", C.c_int32), ("ray_phases", C.c_int32)]
+                ("num_depth_samples", C.c_int32), ("ray_phases", C.c_int32), ("refine_window", C.c_float)]
 
 
 class Profile(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("ms_gn_fwd", "ms_gn_jac", "ms_rows_fwd", "ms_rows_jac")] + \
                [(n, C.c_int64) for n in ("rows_gn_fwd", "rows_gn_jac", "rows_fwd", "rows_jac",
-                                         "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac", "rows_gn_inball")]
+                                         "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac", "rows_gn_inball",
+                                         "rows_gn_refine", "n_gn_refine")] + [("ms_gn_refine", C.c_double)]
 
 
 class FrameParams(C.Structure):
@@ -80,6 +81,8 @@ def lib():
     L.dspslam_last_error.restype = C.c_char_p
     L.dspslam_launch_count.restype = i64
     L.dspslam_launch_count.argtypes = [vp]
+    L.dspslam_mode_available.restype = C.c_int
+    L.dspslam_mode_available.argtypes = [vp, C.c_int]
     L.dspslam_create.restype = C.c_int
     L.dspslam_create.argtypes = [C.POINTER(DecoderDesc), C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                  C.c_int, C.POINTER(C.c_void_p)]

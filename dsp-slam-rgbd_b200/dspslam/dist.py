@@ -6,7 +6,8 @@
 * The mesh grid (`reconstruct/optimizer.py:224-228`) is split into contiguous slabs of linear voxel indices -
   slabs of the slowest axis x, the contiguous equivalent of the z-slabs the reference layout would make strided
   (`reconstruct/utils.py:106`: z is the fastest axis) - evaluated with `dspslam_grid_sdf(i0, i1)` on each rank
-  and gathered with one all-gather (NCCL over NVLink on the B200 box; gloo in the CPU tests).
+  and gathered with all-gathers that overlap the remaining slab kernels (NCCL over NVLink on the B200 box; gloo in
+  the CPU tests).
 """
 from __future__ import annotations
 
@@ -34,20 +35,57 @@ def _world(group):
     return dist.get_rank(group), dist.get_world_size(group)
 
 
-def grid_sdf_sharded(engine, code, G, coord_mode="reference_shear", mode=None, group=None):
-    """(G, G, G) SDF volume on every rank; each rank evaluates one slab, one all-gather assembles it.
-    `engine` needs `.grid_sdf(code, G, i0, i1, coord_mode=, out=, mode=)` and `.torch`/`.device` (dspslam.Engine)."""
+def piece_ranges(total, rank, world, pieces):
+    """The volume is cut into `pieces` contiguous pieces, each piece into `world` equal sub-slabs: rank r evaluates
+    sub-slab r of every piece, and ONE all-gather per piece assembles a contiguous range of the final volume.
+    Returns (per, [(lo, hi, out_lo)] per piece): `per` voxels per sub-slab (padded), this rank's global index range
+    clipped to `total`, and the first index of the piece in the padded output buffer."""
+    per = (total + pieces * world - 1) // (pieces * world)
+    out = []
+    for j in range(pieces):
+        lo = min((j * world + rank) * per, total)
+        out.append((lo, min(lo + per, total), j * world * per))
+    return per, out
+
+
+def grid_sdf_sharded(engine, code, G, coord_mode="reference_shear", mode=None, group=None, pieces=4, timing=None):
+    """(G, G, G) SDF volume on every rank (reconstruct/optimizer.py:224-228 over the ranks).  With W > 1 ranks the
+    grid kernel runs piece by piece and the all-gather of piece j (async, NCCL's own stream) overlaps the kernel of
+    piece j + 1, so only the last piece's gather is exposed.  `engine` needs `.grid_sdf(code, G, i0, i1, coord_mode=,
+    out=, mode=)` and `.device` (dspslam.Engine).  `timing`: optional dict, filled with CUDA-event milliseconds of
+    the slab kernels and of the whole call (device timed)."""
     import torch
     import torch.distributed as dist
     rank, world = _world(group)
     total = G ** 3
-    lo, hi, per = slab_range(total, rank, world)
-    full = torch.empty(per * world, dtype=torch.float32, device=engine.device)
-    mine = full[rank * per: rank * per + per]
-    if hi > lo:
-        engine.grid_sdf(code, G, i0=lo, i1=hi, coord_mode=coord_mode, out=mine[: hi - lo], mode=mode)
-    if world > 1:
-        dist.all_gather_into_tensor(full, mine.clone() if full.device.type == "cpu" else mine, group=group)
+    if world == 1:
+        pieces = 1
+    per, ranges = piece_ranges(total, rank, world, pieces)
+    full = torch.empty(per * world * pieces, dtype=torch.float32, device=engine.device)
+    on_gpu = full.device.type == "cuda"
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)] if (timing is not None and on_gpu) else None
+    if ev:
+        ev[0].record()
+    works = []
+    for lo, hi, out_lo in ranges:
+        mine = full[out_lo + rank * per: out_lo + (rank + 1) * per]
+        if hi > lo:
+            engine.grid_sdf(code, G, i0=lo, i1=hi, coord_mode=coord_mode, out=mine[: hi - lo], mode=mode)
+        if world > 1:
+            works.append(dist.all_gather_into_tensor(full[out_lo: out_lo + world * per], mine if on_gpu else mine.clone(),
+                                                     group=group, async_op=True))
+    if ev:
+        ev[1].record()            # behind the last slab kernel, in front of the waits: the compute part alone
+    for w in works:
+        w.wait()
+    if timing is not None and on_gpu:
+        end = torch.cuda.Event(enable_timing=True)
+        end.record()
+        end.synchronize()
+        timing["ms_compute"] = ev[0].elapsed_time(ev[1])
+        timing["ms_total"] = ev[0].elapsed_time(end)
+        timing["ms_allgather_exposed"] = ev[1].elapsed_time(end)
+        timing["pieces"] = pieces
     return full[:total].view(G, G, G)
 
 

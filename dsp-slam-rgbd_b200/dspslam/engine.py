@@ -11,7 +11,7 @@ from dataclasses import dataclass
 import numpy as np
 
 from . import _native as N
-from .packer import check_supported, effective_weights
+from .packer import check_supported, check_variant, effective_weights
 
 _MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE_TC: N.MODE_TC,
           "mix_fwd_tc": 2, "mix_jac_tc": 3}     # diagnostic mixes (tools/free_run_stats.py)
@@ -56,6 +56,7 @@ class Engine:
                                    (device if isinstance(device, int) else torch.device(device).index or 0))
         self.mode = _MODES[mode]
         sd = decoder.state_dict() if hasattr(decoder, "state_dict") else decoder
+        check_variant(decoder, sd)
         layers = effective_weights(sd)
         self.code_len = check_supported(layers)
         self.in_dim = self.code_len + 3
@@ -66,6 +67,12 @@ class Engine:
         N.check(self.lib.dspslam_create(C.byref(desc), Wp, bp, self.device.index, C.byref(h)), "dspslam_create")
         self._h = h
         self._keep = layers
+        self._pinned = {}
+        if self.mode != N.MODE_FP32 and not self.lib.dspslam_mode_available(h, N.MODE_TC):
+            why = (self.lib.dspslam_last_error() or b"").decode()
+            self.close()
+            raise N.NativeError("mode 'tc' is not available for this decoder: %s.  Construct the Optimizer / Engine with "
+                                "mode='fp32' (FFMA kernels) for it." % why)
 
     # -- lifetime -----------------------------------------------------------------------------
     def close(self):
@@ -93,6 +100,24 @@ class Engine:
         return {n: getattr(p, n) for n, _ in N.Profile._fields_}
 
     # -- helpers ------------------------------------------------------------------------------
+    def _staging(self, nbytes):
+        """Pinned host staging for one batch.  `cudaHostAlloc` costs about as much as a whole single-detection call,
+        so the buffers are kept per size class (powers of two) and per host thread, and handed out round-robin from
+        a ring of four: a batch stays valid while the next three are packed (callers that keep more JointBatch
+        objects alive at once pass pinned=False or pack into their own buffers)."""
+        import threading
+        t = self.torch
+        cls = 1 << max(12, int(nbytes - 1).bit_length())
+        key = (threading.get_ident(), cls)
+        ring = self._pinned.setdefault(key, [[], 0])
+        if len(ring[0]) < 4:
+            ring[0].append(t.empty(cls, dtype=t.uint8, pin_memory=True))
+            buf = ring[0][-1]
+        else:
+            buf = ring[0][ring[1] % 4]
+            ring[1] += 1
+        return buf[:nbytes]
+
     def _stream(self):
         return C.c_void_p(self.torch.cuda.current_stream(self.device).cuda_stream)
 
@@ -172,9 +197,11 @@ class Engine:
             cap_v, cap_t = nv, nf
 
     # -- Gauss-Newton --------------------------------------------------------------------------
-    def pack_joint(self, dets, pinned=True):
+    def pack_joint(self, dets, pinned=True, cached=False):
         """Concatenate detections into one (pinned) host blob.  `dets`: iterable of dicts/tuples with
-        t_cam_obj (4,4), pts (M,3), rays (N,3), depth (n_fg,), optional code."""
+        t_cam_obj (4,4), pts (M,3), rays (N,3), depth (n_fg,), optional code.  cached=True takes the blob from the
+        engine's ring of pinned staging buffers (the one-shot path of gn_joint: valid until three more batches have
+        been packed by this thread); otherwise a fresh pinned allocation the caller owns."""
         t = self.torch
         L = self.code_len
         T, P, R, Dp, Cd = [], [], [], [], []
@@ -208,7 +235,7 @@ class Engine:
             offs[name] = cur
             cur = _align(cur + nbytes)
         offs["io_end"] = cur
-        host = t.empty(cur, dtype=t.uint8, pin_memory=pinned)
+        host = self._staging(cur) if (pinned and cached) else t.empty(cur, dtype=t.uint8, pin_memory=pinned)
         hb = host.numpy()
 
         def put(name, arr):
@@ -246,7 +273,8 @@ class Engine:
         io[o["codes"]: o["codes"] + 4 * L * B].copy_(io[o["codes0"]: o["codes0"] + 4 * L * B])
         prm = N.JointParams(params["k1"], params["k2"], params["k3"], params["k4"], params["b1"], params["b2"],
                             params["lr"], params["s_damp"], params["cut_off"], params["num_iterations"],
-                            params["num_depth_samples"], int(params.get("ray_phases", 0)))
+                            params["num_depth_samples"], int(params.get("ray_phases", 0)),
+                            float(params.get("refine_window", 0.0)))
         dbg = None
         if debug:
             dbg = t.zeros((max(1, params["num_iterations"]), B, N.DBG_STRIDE), dtype=t.float32, device=self.device)
@@ -274,7 +302,7 @@ class Engine:
 
     def gn_joint(self, dets, params, mode=None, debug=False):
         """Host arrays in, host arrays out (the call `reconstruct_object(s)` makes)."""
-        batch = self.upload_joint(self.pack_joint(dets))
+        batch = self.upload_joint(self.pack_joint(dets, cached=True))
         dbg = self.run_joint(batch, params, mode=mode, debug=debug)
         return self.download_joint(batch, dbg)
 
@@ -307,15 +335,26 @@ class Engine:
         B = T.shape[0]
         pts_off = np.zeros(B + 1, np.int32)
         pts_off[1:] = np.cumsum([p.shape[0] for p in P])
-        d_off = t.from_numpy(pts_off).to(self.device)
-        d_pts = t.from_numpy(np.concatenate(P)).to(self.device)
-        d_T = t.from_numpy(T).to(self.device)
-        d_sc = t.from_numpy(sc).to(self.device)
-        d_code = t.from_numpy(np.ascontiguousarray(Cd)).to(self.device)
+        # one pinned staging blob, one H2D copy (five pageable copies used to cost more than the five GN iterations)
+        pts_all = np.concatenate(P)
+        offs, cur = {}, 0
+        for name, arr in (("off", pts_off), ("pts", pts_all), ("T", T), ("sc", sc), ("code", np.ascontiguousarray(Cd))):
+            offs[name] = cur
+            cur = _align(cur + arr.nbytes)
+        host = self._staging(cur)
+        hb = host.numpy()
+        for name, arr in (("off", pts_off), ("pts", pts_all), ("T", T), ("sc", sc), ("code", np.ascontiguousarray(Cd))):
+            b8 = np.ascontiguousarray(arr).view(np.uint8).reshape(-1)
+            hb[offs[name]: offs[name] + b8.size] = b8
+        blob = host.to(self.device, non_blocking=True)
+        base = blob.data_ptr()
         dbg = t.zeros((max(1, num_iterations), B, 64), dtype=t.float32, device=self.device) if debug else None
         N.check(self.lib.dspslam_gn_pose_only(
-            self._h, self._stream(), self._mode(mode), num_iterations, B, d_off.data_ptr(), d_pts.data_ptr(),
-            int(pts_off[-1]), int(max(p.shape[0] for p in P)), d_sc.data_ptr(), d_code.data_ptr(), d_T.data_ptr(),
+            self._h, self._stream(), self._mode(mode), num_iterations, B, base + offs["off"], base + offs["pts"],
+            int(pts_off[-1]), int(max(p.shape[0] for p in P)), base + offs["sc"], base + offs["code"], base + offs["T"],
             dbg.data_ptr() if dbg is not None else None), "dspslam_gn_pose_only")
-        out = d_T.cpu().numpy().reshape(B, 4, 4)
+        lo = offs["T"]
+        host[lo: lo + 64 * B].copy_(blob[lo: lo + 64 * B], non_blocking=True)
+        t.cuda.current_stream(self.device).synchronize()
+        out = hb[lo: lo + 64 * B].view(np.float32).reshape(B, 4, 4).copy()
         return (out, dbg.cpu().numpy()) if debug else out

@@ -37,6 +37,23 @@ def effective_weights(state_dict):
     return layers
 
 
+def check_variant(decoder, state_dict):
+    """Raise ValueError for DeepSDF variants whose arithmetic the library does not implement (evaluating them as the
+    plain net would give silently wrong SDFs): `use_tanh` (the reference applies tanh twice then,
+    deep_sdf_decoder.py:97-110), LayerNorm layers (`bnK.*` parameters: weight_norm=False with norm_layers), an extra
+    xyz re-injection (`xyz_in_all`), active dropout is irrelevant in eval mode."""
+    if getattr(decoder, "use_tanh", False):
+        raise ValueError("unsupported decoder variant: use_tanh=True (double tanh) is not implemented")
+    if getattr(decoder, "xyz_in_all", False):
+        raise ValueError("unsupported decoder variant: xyz_in_all=True is not implemented")
+    bad = [k for k in state_dict if k.split(".")[-2 if "." in k else 0].startswith("bn") or k.startswith("bn") or ".bn" in k]
+    if bad:
+        raise ValueError("unsupported decoder variant: LayerNorm parameters %s (weight_norm=False with norm_layers)" % bad[:3])
+    li = getattr(decoder, "latent_in", None)
+    if li is not None and tuple(li) != (4,):
+        raise ValueError("unsupported decoder variant: latent_in=%s (supported: [4])" % (list(li),))
+
+
 def check_supported(layers):
     """Raise ValueError unless the layer shapes are the 8x512 latent_in=[4] family; returns code_len."""
     if len(layers) != 9:

@@ -63,8 +63,11 @@ def _resolve_engine(decoder=None, configs=None):
 
 
 class Optimizer(object):
-    def __init__(self, decoder, configs, mode="tc", device=None, verbose=False, ray_phases=0):
+    def __init__(self, decoder, configs, mode="tc", device=None, verbose=False, ray_phases=0, refine_window=0.0):
         self.decoder = decoder
+        # tensor-core mode: ray samples the FP16-operand pass leaves within refine_window * cut_off of a decision
+        # threshold of the render term get a second, FP32-grade evaluation (0 = library default 0.1, < 0 = off)
+        self.refine_window = refine_window
         # render term: 1 = evaluate every in-ball ray sample (as the reference does), 2..4 = stop rays at their
         # first fully occupied sample (bit-identical, fewer decoder queries), 0 = let the library choose
         self.ray_phases = ray_phases
@@ -92,7 +95,8 @@ class Optimizer(object):
     def _params(self):
         return dict(k1=self.k1, k2=self.k2, k3=self.k3, k4=self.k4, b1=self.b1, b2=self.b2, lr=self.lr,
                     s_damp=self.s_damp, cut_off=self.cut_off, num_iterations=self.num_iterations_joint_optim,
-                    num_depth_samples=self.num_depth_samples, ray_phases=self.ray_phases)
+                    num_depth_samples=self.num_depth_samples, ray_phases=self.ray_phases,
+                    refine_window=self.refine_window)
 
     # ---- pose only (stereo+LiDAR re-observation), optimizer.py:46-87 ------------------------
     def estimate_pose_cam_obj(self, t_co_se3, scale, pts, code):

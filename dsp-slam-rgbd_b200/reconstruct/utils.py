@@ -105,6 +105,23 @@ def create_voxel_grid(vol_dim=128, coord_mode="reference_shear"):
     return out
 
 
+def convert_sdf_voxels_to_mesh(pytorch_3d_sdf_tensor):
+    """Same name, argument and return convention as the reference (`reconstruct/utils.py:119-140`): a (n, n, n) SDF
+    volume (torch tensor, host or device, or numpy array) -> (vertices (nv, 3) float32 in [-1, 1]^3, faces (nf, 3)
+    int32) at level 0 with voxel size 2 / (n - 1).  The reference runs skimage's `marching_cubes_lewiner` on the CPU;
+    here the volume is meshed on the GPU by `dspslam_marching_cubes` (csrc/mesh.cu) through the process's engine -
+    same vertex set, this repository's own triangulation table (dspslam/mesh.py; face topology against Lewiner's
+    is unpinned: skimage is absent from the image)."""
+    import torch
+    from dspslam.mesh import sdf_grid_to_mesh
+    from reconstruct.optimizer import _resolve_engine
+    eng = _resolve_engine()
+    sdf = pytorch_3d_sdf_tensor if isinstance(pytorch_3d_sdf_tensor, torch.Tensor) else torch.from_numpy(
+        np.ascontiguousarray(pytorch_3d_sdf_tensor, dtype=np.float32))
+    verts, faces = sdf_grid_to_mesh(eng, sdf.detach().to(eng.device))
+    return verts, faces
+
+
 def write_mesh_to_ply(v, f, ply_filename_out):
     """Binary little-endian PLY with float32 x,y,z vertices and int32 triangle lists."""
     v = np.ascontiguousarray(v, dtype="<f4")

@@ -31,8 +31,10 @@
  *     last error on the calling thread is returned by dspslam_last_error().
  *   - no exception crosses the ABI; nothing is retained from caller memory after return
  *     (asynchronous work is ordered on `stream`).
- *   - a handle may be used from several host threads; calls on one handle serialise
- *     on an internal mutex (the reference serialises on the Python GIL).
+ *   - a handle may be used from several host threads and with different streams; calls on one
+ *     handle serialise on an internal mutex on the host (the reference serialises on the Python GIL)
+ *     and are ordered on the device by an event when consecutive calls arrive on different streams
+ *     (the handle's scratch is shared).
  */
 #ifndef DSPSLAM_H_
 #define DSPSLAM_H_
@@ -43,7 +45,7 @@
 extern "C" {
 #endif
 
-#define DSPSLAM_ABI_VERSION 1
+#define DSPSLAM_ABI_VERSION 2
 
 enum {
     DSPSLAM_OK = 0,
@@ -87,6 +89,10 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
 void dspslam_destroy(dspslam_handle* h);
 const char* dspslam_last_error(void);
 int dspslam_abi_version(void);
+/* 1 if `mode` can run on this handle's decoder, else 0 with the reason in dspslam_last_error(): the tcgen05 path
+ * needs (512 - code_len - 3), rounded up to 16, to be a multiple of its 32-wide K stages (code_len 64 and 32 - the
+ * two lengths the reference's callers handle, src/LocalMapping_util.cc:416-426 - qualify). */
+int dspslam_mode_available(const dspslam_handle* h, int mode);
 /* number of kernels launched by this handle so far (for bench.py's gpu_launches) */
 int64_t dspslam_launch_count(const dspslam_handle* h);
 
@@ -132,6 +138,11 @@ typedef struct {
                                 * 1 evaluates every in-ball sample like the reference; 2..4 stop a ray at its first
                                 * sample with sdf <= -cut_off (occupancy exactly 1, transmittance exactly 0 behind
                                 * it: bit-identical results, fewer decoder queries); 0 lets the library choose. */
+    float refine_window;       /* DSPSLAM_MODE_TC only.  The render term takes decisions at |sdf| = cut_off (occupancy
+                                * clamp and with_grad mask, loss.py:98-102).  A ray sample the FP16-operand forward pass
+                                * leaves within refine_window * cut_off of such a threshold is evaluated a second time
+                                * with hi+lo FP16 operand pairs (FP32-grade) before the per-ray scan, so the selected row
+                                * set follows the FP32 reference.  0 = library default (0.1); < 0 switches it off. */
 } dspslam_joint_params;
 
 /* A batch of B independent detections, concatenated.
@@ -174,6 +185,9 @@ typedef struct {
     int64_t rows_gn_fwd, rows_gn_jac, rows_fwd, rows_jac;
     int64_t n_gn_fwd, n_gn_jac, n_rows_fwd, n_rows_jac;
     int64_t rows_gn_inball; /* in-ball ray samples of the GN loop (what the reference evaluates; >= rows_gn_fwd) */
+    int64_t rows_gn_refine; /* ray samples evaluated a second time at FP32 grade (joint_params.refine_window)     */
+    int64_t n_gn_refine;
+    double ms_gn_refine;
 } dspslam_profile;
 int dspslam_profile_enable(dspslam_handle* h, int on);
 int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out);

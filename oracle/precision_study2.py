@@ -40,7 +40,7 @@ class EmuDecoder(orc.OracleDecoder):
     def __init__(self, sd, spec):
         super().__init__(sd)
         self.spec = spec
-        self.Wv = {m: [RND[m](w) for w in self.W] for m in set((spec[0], spec[2]))}
+        self.Wv = {m: [RND[m](w) for w in self.W] for m in set((spec[0], spec[2]) + ((spec[7],) if len(spec) > 5 else ()))}
 
     def _fwd(self, inp, wm, am, keep):
         W = self.Wv[wm]
@@ -69,7 +69,18 @@ class EmuDecoder(orc.OracleDecoder):
         if x.shape[0] == 0:
             return np.zeros((0,), np.float32)
         inp = np.concatenate([np.broadcast_to(code, (x.shape[0], code.shape[0])), x], axis=-1)
-        return self._fwd(inp, self.spec[0], self.spec[1], False)[0][:, 0]
+        s = self._fwd(inp, self.spec[0], self.spec[1], False)[0][:, 0]
+        if len(self.spec) > 5:
+            # second, FP32-grade evaluation of the rows the FP16 pass leaves within eps of a decision threshold
+            # ('edge': | |s| - th | < eps) or anywhere inside the widened band ('band': |s| < th + eps)
+            kind, eps, th = self.spec[5], self.spec[6], 0.01
+            m = (np.abs(np.abs(s) - th) < eps) if kind == "edge" else (np.abs(s) < th + eps)
+            self.refined = getattr(self, "refined", 0) + int(m.sum())
+            self.total = getattr(self, "total", 0) + int(m.size)
+            if m.any():
+                s = s.copy()
+                s[m] = self._fwd(inp[m], self.spec[7], self.spec[8], False)[0][:, 0]
+        return s
 
     def sdf_jacobian(self, code, xyz, max_batch=1 << 16):
         code = np.asarray(code, np.float32)
@@ -100,6 +111,13 @@ VARIANTS = {
     "F W a | J W a g": ("2", "1", "2", "1", "1"),
     "F W A | J W A G": ("2", "2", "2", "2", "2"),
     "F W a | J W A G": ("2", "1", "2", "2", "2"),
+    "F tc+edge5e-4 | J fp32": ("1", "1", "", "", "", "edge", 5e-4, "", ""),
+    "F tc+band5e-4 | J fp32": ("1", "1", "", "", "", "band", 5e-4, "", ""),
+    "F tc+edge5e-4(WA) | J tc": ("1", "1", "1", "1", "1", "edge", 5e-4, "2", "2"),
+    "F tc+edge5e-4(WA) | J W a g": ("1", "1", "2", "1", "1", "edge", 5e-4, "2", "2"),
+    "F tc+band5e-4(WA) | J W a g": ("1", "1", "2", "1", "1", "band", 5e-4, "2", "2"),
+    "F tc+band5e-4(WA) | J tc": ("1", "1", "1", "1", "1", "band", 5e-4, "2", "2"),
+    "F tc+band5e-4(WA) | J W A G": ("1", "1", "2", "2", "2", "band", 5e-4, "2", "2"),
 }
 
 
@@ -157,6 +175,8 @@ def main():
                                                    np.median(E[..., 1]), np.quantile(E[..., 1], .95), E[..., 1].max(),
                                                    np.median(E[..., 2]), np.quantile(E[..., 2], .95), E[..., 2].max()),
               flush=True)
+        if hasattr(dec, "refined"):
+            print("    refined rows: %d of %d forward rows (%.2f %%)" % (dec.refined, dec.total, 100. * dec.refined / dec.total), flush=True)
 
 
 if __name__ == "__main__":

@@ -57,9 +57,10 @@ def _worker(rank, world, port, q):
     from dspslam.dist import grid_sdf_sharded, reconstruct_sharded, shard_range
     ok = True
     for G in (4, 5, 9):          # 125 and 729 voxels do not divide by 2: padded slabs
-        vol = grid_sdf_sharded(_StubEngine(), np.array([3.0], np.float32), G)
-        ok &= vol.shape == (G, G, G)
-        ok &= bool(torch.equal(vol.reshape(-1), torch.arange(G ** 3, dtype=torch.float32) * 0.5 + 3.0))
+        for pieces in (4, 1, 3):  # one all-gather per piece, overlapped with the next piece's kernel on the GPU box
+            vol = grid_sdf_sharded(_StubEngine(), np.array([3.0], np.float32), G, pieces=pieces)
+            ok &= vol.shape == (G, G, G)
+            ok &= bool(torch.equal(vol.reshape(-1), torch.arange(G ** 3, dtype=torch.float32) * 0.5 + 3.0))
     dets = list(range(11))
     outs = reconstruct_sharded(_StubOptimizer(rank), dets)
     ok &= len(outs) == 11

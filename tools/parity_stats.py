@@ -1,0 +1,112 @@
+"""Parity statistics of a library mode against vectors produced by the UNMODIFIED reference (tests/golden/,
+oracle/make_goldens*.py) - the numbers behind north_star's ">= 95 % of reference objects within tolerance".
+
+  jacobian     queries_wfit.npz: fraction of the 67-entry Jacobian rows / of single entries within 1e-3 (tensor-core
+               modes) or 1e-5 (FP32 mode) of `get_batch_sdf_jacobian`, max |SDF error|
+  steps        bulk_c1.npz (128 KITTI-style cars x 10 iterations): ONE Gauss-Newton step from the reference's own
+               state at iteration e against the reference's state at e + 1 (teacher forcing: the free-running
+               trajectory is chaotic in the reference itself, tests/golden/noise_floor.json); a step is within
+               tolerance when |dt| < 1 cm, rotation < 0.1 deg and |dcode| / max(|code|, 0.1) < 1e-2
+  objects      fraction of objects whose LAST step (the state the caller receives) is within tolerance, and
+               fraction with every one of the 10 steps within tolerance
+
+Used by bench.py (`parity` key), tests/test_gpu_parity_bulk.py and from the command line:
+    python tools/parity_stats.py [mode ...]"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _load(name):
+    with np.load(os.path.join(GOLD, name)) as z:
+        return {k: z[k] for k in z.files}
+
+
+def joint_params(cfg, iters):
+    j = cfg.optimizer.joint_optim
+    return dict(k1=j.k1, k2=j.k2, k3=j.k3, k4=j.k4, b1=j.b1, b2=j.b2, lr=j.learning_rate, s_damp=j.scale_damping,
+                cut_off=cfg.optimizer.cut_off_threshold, num_iterations=iters,
+                num_depth_samples=cfg.optimizer.num_depth_samples)
+
+
+def jacobian_stats(eng, mode):
+    mode = mode.split(":")[0]
+    g = _load("queries_wfit.npz")
+    tol = 1e-5 if mode == "fp32" else 1e-3
+    s, jac = eng.sdf_jac(g["code"], g["xyz"], mode=mode)
+    err = np.abs(jac.cpu().numpy() - g["jac"])
+    return {"tol": tol, "rows": int(err.shape[0]), "rows_within": float((err.max(axis=1) <= tol).mean()),
+            "entries_within": float((err <= tol).mean()), "rms": float(np.sqrt((err ** 2).mean())),
+            "sdf_max_err": float(np.abs(s.cpu().numpy() - g["sdf_j"]).max())}
+
+
+def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
+    from dspslam import synth
+    b = _load(which)
+    mono = "c3" in which
+    cfg = synth.redwood_config() if mono else synth.kitti_config()
+    make = synth.make_mono_detection if mono else synth.make_kitti_detection
+    ks = [k for k in range(min(n_objects, b["T_oc"].shape[0])) if b["is_good"][k]]
+    dets = [make(k) for k in ks]
+    for k, d in zip(ks, dets):      # the generator must still produce the inputs the reference ran on
+        chk = float(sum(np.asarray(d[n], np.float64).sum() for n in ("t_cam_obj", "pts", "rays", "depth")))
+        assert abs(chk - float(b["in_sum"][k])) < 1e-6 * max(1.0, abs(chk)), "synthetic generator drifted (object %d)" % k
+    n_it = b["T_oc"].shape[1]
+    prm = joint_params(cfg, 1)
+    if mode.endswith(":norefine"):          # tensor-core forward pass without the FP32-grade second evaluation
+        prm["refine_window"] = -1.0
+    mode = mode.split(":")[0]
+    E = np.zeros((len(ks), n_it, 3))
+    for e in range(n_it):
+        batch = []
+        for k, d in zip(ks, dets):
+            T_co = np.linalg.inv(b["T_oc"][k, e].astype(np.float64)).astype(np.float32)
+            batch.append((T_co, d["pts"], d["rays"], d["depth"], b["code_it"][k, e]))
+        res = eng.gn_joint(batch, prm, mode=mode)
+        for i, k in enumerate(ks):
+            if e + 1 < n_it:
+                Tn, cn = np.linalg.inv(b["T_oc"][k, e + 1].astype(np.float64)), b["code_it"][k, e + 1]
+            else:
+                Tn, cn = b["t_cam_obj"][k], b["code"][k]
+            if res.status[i] != 0:
+                E[i, e] = (1.0, 90.0, 1.0)
+                continue
+            dt, ang, _ = synth.pose_errors(res.t_cam_obj[i], Tn)
+            E[i, e] = (dt, ang, np.linalg.norm(res.code[i] - cn) / max(np.linalg.norm(cn), 0.1))
+    ok = (E[..., 0] < 1e-2) & (E[..., 1] < 0.1) & (E[..., 2] < 1e-2)
+    q = lambda a, p: float(np.quantile(a, p))
+    return {"objects": len(ks), "steps": int(ok.size), "steps_within": float(ok.mean()),
+            "objects_last_step_within": float(ok[:, -1].mean()), "objects_all_steps_within": float(ok.all(axis=1).mean()),
+            "dt_m": {"median": q(E[..., 0], .5), "q95": q(E[..., 0], .95), "max": float(E[..., 0].max())},
+            "rot_deg": {"median": q(E[..., 1], .5), "q95": q(E[..., 1], .95), "max": float(E[..., 1].max())},
+            "code_rel": {"median": q(E[..., 2], .5), "q95": q(E[..., 2], .95), "max": float(E[..., 2].max())},
+            "tolerance": "1 cm / 0.1 deg / 1e-2 per teacher-forced GN step", "golden": which}
+
+
+def parity(eng, mode, n_objects=128):
+    out = {"mode": mode}
+    if not str(mode).startswith("mix"):
+        out["jacobian"] = jacobian_stats(eng, mode)
+    if os.path.isfile(os.path.join(GOLD, "bulk_c1.npz")):
+        out["c1"] = step_stats(eng, mode, n_objects)
+    if os.path.isfile(os.path.join(GOLD, "bulk_c3.npz")):
+        out["c3"] = step_stats(eng, mode, 32, "bulk_c3.npz")
+    return out
+
+
+def main():
+    sys.path[:0] = [os.path.join(ROOT, "dsp-slam-rgbd_b200"), ROOT]
+    from dspslam import synth
+    from dspslam.engine import Engine
+    eng = Engine(synth.load_wfit())
+    for mode in sys.argv[1:] or ["fp32", "tc"]:
+        print(json.dumps(parity(eng, mode)), flush=True)
+
+
+if __name__ == "__main__":
+    main()
