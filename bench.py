@@ -309,7 +309,7 @@ def ours_arm(args, rank, world, local_rank):
         "metric": METRIC, "value": value, "unit": "objects/s", "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None,
-        "dtype": "f16 operands, f32 accumulate (tcgen05)" if args.mode == "tc" else "f32",
+        "dtype": "f16 operands, f32 accumulate (tcgen05)" if args.mode != "fp32" else "f32",
         "data": "synthetic",
         "config": shared_config(args.mode, args.ray_phases),
         "e2e": {"value": total_obj / e2e_s, "unit": "objects/s", "h2d_bytes_per_step": int(batch.h2d_bytes),
@@ -467,7 +467,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default="tc", choices=["tc", "fp32"])
+    ap.add_argument("--mode", default="tc", choices=["tc", "tc_fast", "fp32"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--skip-configs", action="store_true", help="skip the c1 / c4 / c5 / parity legs")
     ap.add_argument("--ray-phases", type=int, default=0,

@@ -218,7 +218,7 @@ int64_t dspslam_launch_count(const dspslam_handle* h) { return h ? h->launches :
 int dspslam_mode_available(const dspslam_handle* h, int mode) {
     if (!h) { g_err = "null handle"; return 0; }
     if (mode == DSPSLAM_MODE_FP32) return 1;
-    if (mode != DSPSLAM_MODE_TC) { g_err = "unknown mode"; return 0; }
+    if (mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) { g_err = "unknown mode"; return 0; }
     if (!h->tc_ready) { g_err = h->tc_why; return 0; }
     return 1;
 }
@@ -290,11 +290,11 @@ void dspslam_destroy(dspslam_handle* h) {
 static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
                    float* sdf_out, float* jac_out) {
     if (!h || n < 0) return fail(DSPSLAM_E_BADARG, "null/negative argument");
-    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) return fail(DSPSLAM_E_BADARG, "bad mode");
     if (n == 0) return 0;                       // empty query: nothing to do (pointers may be null)
     if (!code || !xyz || !sdf_out) return fail(DSPSLAM_E_BADARG, "null argument");
     if (n > ((int64_t)1 << 31) - 256) return fail(DSPSLAM_E_BADARG, "n too large for one call");
-    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
+    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     float* c0 = h->lat;
     float* c4 = h->lat + HID;
     launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
@@ -305,7 +305,8 @@ static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
         else launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, sdf_out, S(stream));
         ++nl;
     } else {
-        if (jac_out) nl += tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
+        if (jac_out) nl += tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out,
+                                             mode == DSPSLAM_MODE_TC ? 1 : 0, S(stream));
         else nl += tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
     }
     prof_end(h, pp, S(stream));
@@ -353,9 +354,9 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     if (i0 < 0 || i1 < i0 || i1 > total) return fail(DSPSLAM_E_BADARG, "bad index range");
     if (coord_mode != DSPSLAM_GRID_REFERENCE_SHEAR && coord_mode != DSPSLAM_GRID_LATTICE)
         return fail(DSPSLAM_E_BADARG, "bad coord_mode");
-    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) return fail(DSPSLAM_E_BADARG, "bad mode");
     if (i1 == i0) return 0;
-    if (mode == DSPSLAM_MODE_TC && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
+    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     StreamOrder so(h, stream);
@@ -394,9 +395,10 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                   int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
                   const float* scale_in, int32_t* status_out, float* loss_out, float* dbg_out, int dbg_stride) {
     // diagnostic mixes (not in the public header): 2 = tensor-core forward samples + FP32 Jacobian rows, 3 = the reverse
-    if (mode < 0 || mode > 3) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode < 0 || mode > 4) return fail(DSPSLAM_E_BADARG, "bad mode");
     if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
-    const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2), jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3);
+    const bool fast = (mode == DSPSLAM_MODE_TC_FAST);
+    const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2 || fast), jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3 || fast);
     if (B <= 0 || B > 65535) return fail(DSPSLAM_E_BADARG, "B must be in 1..65535");
     if (iters < 0) return fail(DSPSLAM_E_BADARG, "negative iteration count");
     const int D = prm.D;
@@ -424,8 +426,9 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.phase = 0;
 
     // second, FP32-grade evaluation of the ray samples next to a decision threshold (tensor-core forward pass only)
-    const bool refine = fwd_tc && !prm.pose_only && refine_window >= 0.f;
-    w.refine_eps = refine ? (refine_window > 0.f ? refine_window : 0.1f) * prm.th : 0.f;
+    const bool refine = fwd_tc && !fast && !prm.pose_only && refine_window >= 0.f;
+    w.jac_wsplit = (jac_tc && !fast) ? 1 : 0;
+    w.refine_eps = refine ? (refine_window > 0.f ? refine_window : 0.05f) * prm.th : 0.f;
     const size_t rgroups_max = refine ? (size_t)(((int64_t)max_rays * D + REFINE_ROWS - 1) / REFINE_ROWS) : 0;
     size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
     if ((size_t)B * rgroups_max + 1 > max_tiles) max_tiles = (size_t)B * rgroups_max + 1;
@@ -676,6 +679,16 @@ int dspslam_pg_oplus(dspslam_handle* h, void* stream, double* vertices, const do
     StreamOrder so(h, stream);
     return check_launch(h, launch_pg_oplus(vertices, updates, n, S(stream)), "dspslam_pg_oplus");
 }
+
+#ifdef DSP_TC_TRACE
+// debug builds only (tools/trace_jac.py): the event log CTA 0 of the last GN Jacobian launch left in the park buffer
+int dspslam_debug_trace(dspslam_handle* h, long long* out_host, int n) {
+    DeviceGuard g(h->device);
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out_host, h->dec.tc_park + (size_t)200 * 128 * 68, sizeof(long long) * (size_t)n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+#endif
 
 int dspslam_profile_enable(dspslam_handle* h, int on) {
     if (!h) return fail(DSPSLAM_E_BADARG, "null handle");

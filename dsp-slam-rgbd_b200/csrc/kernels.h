@@ -33,6 +33,7 @@ struct GnWork {
     float4* rrows;        // [total_rays*D]  per object: samples the FP16 forward pass left within refine_eps of a decision
                           //                 threshold (| |s| - th | < eps): x,y,z,dest; re-evaluated by k_tc_refine
     float refine_eps;     // 0: no second evaluation (FP32 mode, or switched off)
+    int jac_wsplit;       // 1: the tcgen05 Jacobian kernel multiplies by hi(W) + lo(W) (two MMA passes per K chunk)
     int* ray_cnt;         // [total_rays]
     int* ray_roff;        // [total_rays]    exclusive row offset of the ray inside its 128-ray chunk
     int* chunk_cnt;       // [B][ray_chunks] rows selected by each chunk of rays, then (scanned) the chunk's first row

@@ -73,6 +73,7 @@ struct TcArgs {
     float* out;
     float* jac_out;
     int n_tiles;
+    int wsplit;              // 1: every hidden K chunk is issued against hi(W) and lo(W) (Jacobian variants of DSPSLAM_MODE_TC)
     // Gauss-Newton work lists
     GnWork w;
 };
@@ -120,9 +121,23 @@ __device__ __forceinline__ void build_pose_row(float* J, float gx, float gy, flo
 
 // MODE 0: rows = xyz array -> out            1: voxel grid, reference shear -> out   2: voxel grid, lattice -> out
 //      3: GN forward (compacted ray samples) 4: xyz array -> sdf + jac               5: GN Jacobian rows -> J^T J partials
+// -DDSP_TC_TRACE: CTA 0 of the GN Jacobian launch (MODE 5) logs (clock64, tag) pairs of its first epilogue warp and of
+// its MMA warp into the unused tail of the park buffer (tools/trace_jac.py reads them): where a layer step's time goes.
+#ifdef DSP_TC_TRACE
+#define TRACE_E(tag) do { if (MODE == 5 && blockIdx.x == 0 && warp == 0 && lane == 0 && te < 3900) { trace[te++] = clock64(); trace[te++] = (tag); } } while (0)
+#define TRACE_M(tag) do { if (MODE == 5 && blockIdx.x == 0 && lane == 0 && tm < 3900) { trace[4096 + tm++] = clock64(); trace[4096 + tm++] = (tag); } } while (0)
+#else
+#define TRACE_E(tag) do { } while (0)
+#define TRACE_M(tag) do { } while (0)
+#endif
+
 template <int MODE>
 __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) {
     using C = Cfg<MODE>;
+#ifdef DSP_TC_TRACE
+    long long* trace = reinterpret_cast<long long*>(a.dec.tc_park + (size_t)200 * TILE_M * PARK_LD);
+    int te = 0, tm = 0;
+#endif
     constexpr bool JAC = C::JAC;
     constexpr int NST = C::NST;
     constexpr bool PAIR = C::PAIR;
@@ -167,6 +182,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     int n_tiles = a.n_tiles;
     if (C::GN) n_tiles = a.w.n_tiles[MODE == 3 ? 0 : 1];
     constexpr int NPROG = JAC ? 2 : 1;
+    const int nrep = (JAC && a.wsplit) ? 2 : 1;
     // tile walk: a pair takes tiles (tb, tb + 1); both CTAs make the same number of trips (the multicast protocol
     // needs them in step), a CTA whose tile index falls behind the list runs the trip with no valid rows
     const int rank = PAIR ? (int)(blockIdx.x & 1u) : 0;
@@ -194,22 +210,24 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         if (++s == NST) { s = 0; ph ^= 1u; }
                     }
                     const uint8_t* src = a.blob + ld.src;        // hidden stages are contiguous in consumption order
+                    const uint8_t* srcl = a.blob + ld.src_lo;    // the same sequence packed from lo(W)
                     for (int n0 = 0; n0 < ld.n; n0 += 256) {
                         const uint32_t bytes = (uint32_t)min(256, (int)ld.n - n0) * 64u;
 #pragma unroll 1
-                        for (int kc = 0; kc < ld.k32; ++kc) {
+                        for (int k2 = 0; k2 < nrep * ld.k32; ++k2) {
+                            const uint8_t* from = (JAC && nrep == 2 && (k2 & 1)) ? srcl : src;
                             mbar_wait(bar_empty(s), ph ^ 1u);
                             if (elect_one()) {
                                 mbar_expect_tx(bar_full(s), bytes);
                                 if (PAIR) {
                                     const uint32_t half = bytes >> 1;
-                                    bulk_g2s_mc(sST + s * STAGE_BYTES + rank * half, src + rank * half, half, bar_full(s), 3);
+                                    bulk_g2s_mc(sST + s * STAGE_BYTES + rank * half, from + rank * half, half, bar_full(s), 3);
                                 } else {
-                                    bulk_g2s(sST + s * STAGE_BYTES, src, bytes, bar_full(s));
+                                    bulk_g2s(sST + s * STAGE_BYTES, from, bytes, bar_full(s));
                                 }
                             }
                             __syncwarp();
-                            src += bytes;
+                            if (nrep == 1 || (k2 & 1)) { src += bytes; srcl += bytes; }
                             if (++s == NST) { s = 0; ph ^= 1u; }
                         }
                     }
@@ -239,6 +257,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
                     mbar_wait(bar_aready, aph);                  // this layer's A operand written, accumulator drained
                     aph ^= 1u;
+                    TRACE_M(100 * p + li);
                     if (ld.xkind) {
                         mbar_wait(bar_full(s), ph);
                         tc_fence_after();
@@ -257,14 +276,15 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         const uint32_t id = idesc_f16(TILE_M, min(256, (int)ld.n - n0));
                         const uint32_t dcol = tmem + n0;
 #pragma unroll 1
-                        for (int kc = 0; kc < ld.k32; ++kc) {
+                        for (int k2 = 0; k2 < nrep * ld.k32; ++k2) {
+                            const int kc = (nrep == 2) ? (k2 >> 1) : k2;     // (hi(W) stage, then lo(W) stage of the same chunk)
                             mbar_wait(bar_full(s), ph);
                             tc_fence_after();
                             if (elect_one()) {
                                 // A: K chunk kc = block kc/2 (16 KB apart), half kc%2 (64 B apart); +32 B per K=16 step
                                 const uint64_t ad = adesc0 + (uint64_t)((kc >> 1) * (A_BLK >> 4) + (kc & 1) * 4);
                                 const uint64_t bd = bdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
-                                umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && kc == 0) ? 0u : 1u);
+                                umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && k2 == 0) ? 0u : 1u);
                                 umma_f16(dcol, ad + 2, bd + 2, id, 1u);
                                 release(bar_empty(s));
                             }
@@ -274,6 +294,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     }
                     if (elect_one()) umma_commit(bar_dfull);     // accumulator of the layer complete
                     __syncwarp();
+                    TRACE_M(1000 + 100 * p + li);
                 }
             }
         }
@@ -370,6 +391,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 mbar_wait(bar_dfull, dph);
                 dph ^= 1u;
                 tc_fence_after();
+                TRACE_E(l);
                 float part = 0.f;
 #pragma unroll 1
                 for (int jp = 0; jp < 4; ++jp) {
@@ -420,6 +442,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 }
                 if (!last) {
                     signal_ready();
+                    TRACE_E(1000 + l);
                 } else {
                     parts[hc * TILE_M + r] = part;
                     tc_fence_before();
@@ -472,12 +495,14 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     store32(col, p);
                 }
                 signal_ready();
+                TRACE_E(1007);
 
                 // steps l = 7..1: D = g_l W_l  -> mask with relu'(a_{l-1}) -> next A
                 for (int l = 7; l >= 1; --l) {
                     mbar_wait(bar_dfull, dph);
                     dph ^= 1u;
                     tc_fence_after();
+                    TRACE_E(100 + l);
                     const bool split = (l == 4);             // columns >= h3 are d/d(input) (latent re-injection)
                     const int h3 = a.dec.h3, h3p = a.dec.h3p;
 #pragma unroll 1
@@ -511,12 +536,14 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         store32(col, p);
                     }
                     signal_ready();
+                    TRACE_E(1100 + l);
                 }
 
                 // step l = 0: D[:, 0..in_dim) = g_0 W_0 ;  jac = (D + gin) / GSCALE
                 mbar_wait(bar_dfull, dph);
                 dph ^= 1u;
                 tc_fence_after();
+                TRACE_E(100);
                 const float inv_s = 1.f / GSCALE;
                 if (hc == 1) {                                // the thread that parked the row's layer-4 gradients
                     uint32_t v0[32], v1[32], v2[32];
@@ -655,12 +682,19 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         part[PART_LOSS + 1] = parts[4] + parts[5] + parts[6] + parts[7];
                     }
                     named_bar_sync(1, EPI_THREADS);
+                    TRACE_E(2000);
                 }
             }
         }
     }
 
     // ---------------- teardown ----------------
+#ifdef DSP_TC_TRACE
+    if (MODE == 5 && blockIdx.x == 0 && lane == 0) {
+        if (warp == 0) trace[4095] = te;
+        if (warp == 9) trace[8191] = tm;
+    }
+#endif
     tc_fence_before();
     __syncthreads();
     if (PAIR) cluster_sync_all();                           // neither CTA leaves while the other may still signal it
@@ -1087,6 +1121,29 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
             }
         }
     }
+    // ---- lo images of the backward program ----
+    auto lo_of = [](float w) -> float { return w - BlobBuilder::h2f(BlobBuilder::f2h(w)); };
+    for (int l = 7; l >= 1; --l) {
+        const int K = (l == 3) ? h3p : HID, Kreal = (l == 3) ? h3 : HID;
+        const float* Wl = W[l];
+        for (int n0 = 0; n0 < HID; n0 += 256) {
+            for (int kb = 0; kb < K / 32; ++kb) {
+                const size_t at = B.sw64(n0, 256, kb, [&](int i, int o) -> float {
+                    return (o < Kreal) ? lo_of(Wl[(size_t)o * HID + i]) : 0.f;
+                });
+                if (n0 == 0 && kb == 0) layers[1][7 - l].src_lo = (uint32_t)at;
+            }
+        }
+    }
+    {
+        const int N0 = (in_dim + 15) & ~15;
+        for (int kb = 0; kb < HID / 32; ++kb) {
+            const size_t at = B.sw64(0, N0, kb, [&](int i, int o) -> float {
+                return (i < in_dim) ? lo_of(W[0][(size_t)o * in_dim + i]) : 0.f;
+            });
+            if (kb == 0) layers[1][7].src_lo = (uint32_t)at;
+        }
+    }
     {
         const int N0 = (in_dim + 15) & ~15;                                                // 80
         layers[1][7].n = (uint16_t)N0; layers[1][7].k32 = HID / 32;
@@ -1163,12 +1220,12 @@ int tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, in
 }
 
 int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
-                      const float* c4, float* sdf_out, float* jac_out, cudaStream_t st) {
+                      const float* c4, float* sdf_out, float* jac_out, int wsplit, cudaStream_t st) {
     using namespace tc;
     k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, dec.tc_xtra1);
     TcArgs a{};
     a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
-    a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
+    a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out; a.wsplit = wsplit;
     a.n_tiles = (int)((n + TILE_M - 1) / TILE_M);
     launch_tc<4>(a, std::min(std::min(a.n_tiles, sm_count), PARK_CTAS), st);
     return 2;
@@ -1195,7 +1252,7 @@ int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st) {
 int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
     TcArgs a{};
-    a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
+    a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w; a.wsplit = w.jac_wsplit;
     launch_tc<5>(a, std::min(sm_count, PARK_CTAS), st);
     return 1;
 }

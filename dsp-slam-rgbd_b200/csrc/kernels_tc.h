@@ -17,7 +17,7 @@ size_t tc_xtra_bytes_per_object();
 int tc_launch_sdf_rows(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, int64_t i0, int G,
                        int src_mode, const float* c0, const float* c4, float* out, cudaStream_t st);
 int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
-                      const float* c4, float* sdf_out, float* jac_out, cudaStream_t st);
+                      const float* c4, float* sdf_out, float* jac_out, int wsplit, cudaStream_t st);
 int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st);
 int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st);
 int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st);

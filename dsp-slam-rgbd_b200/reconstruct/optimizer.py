@@ -66,7 +66,7 @@ class Optimizer(object):
     def __init__(self, decoder, configs, mode="tc", device=None, verbose=False, ray_phases=0, refine_window=0.0):
         self.decoder = decoder
         # tensor-core mode: ray samples the FP16-operand pass leaves within refine_window * cut_off of a decision
-        # threshold of the render term get a second, FP32-grade evaluation (0 = library default 0.1, < 0 = off)
+        # threshold of the render term get a second, FP32-grade evaluation (0 = library default 0.05, < 0 = off)
         self.refine_window = refine_window
         # render term: 1 = evaluate every in-ball ray sample (as the reference does), 2..4 = stop rays at their
         # first fully occupied sample (bit-identical, fewer decoder queries), 0 = let the library choose

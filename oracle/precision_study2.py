@@ -40,7 +40,10 @@ class EmuDecoder(orc.OracleDecoder):
     def __init__(self, sd, spec):
         super().__init__(sd)
         self.spec = spec
-        self.Wv = {m: [RND[m](w) for w in self.W] for m in set((spec[0], spec[2]) + ((spec[7],) if len(spec) > 5 else ()))}
+        need = set((spec[0], spec[2]) + ((spec[7],) if len(spec) > 5 else ()))
+        if need & {"f", "b"}:
+            need = (need - {"f", "b"}) | {"1", "2"}
+        self.Wv = {m: [RND[m](w) for w in self.W] for m in need}
 
     def _fwd(self, inp, wm, am, keep):
         W = self.Wv[wm]
@@ -86,8 +89,9 @@ class EmuDecoder(orc.OracleDecoder):
         code = np.asarray(code, np.float32)
         x = np.asarray(xyz, np.float32)
         inp = np.concatenate([np.broadcast_to(code, (x.shape[0], code.shape[0])), x], axis=-1)
-        out, acts = self._fwd(inp, self.spec[2], self.spec[3], True)
-        W = self.Wv[self.spec[2]]
+        jw = self.spec[2]
+        out, acts = self._fwd(inp, "1" if jw == "b" else ("2" if jw == "f" else jw), self.spec[3], True)
+        W = self.Wv["2" if jw == "b" else ("1" if jw == "f" else jw)]      # 'f' / 'b': hi+lo weights in the forward / backward sweep only
         gm = RND[self.spec[4]]
         g = (1 - out * out).astype(np.float32) @ self.W[self.n_layers - 1]
         g_in = 0
@@ -111,6 +115,11 @@ VARIANTS = {
     "F W a | J W a g": ("2", "1", "2", "1", "1"),
     "F W A | J W A G": ("2", "2", "2", "2", "2"),
     "F W a | J W A G": ("2", "1", "2", "2", "2"),
+    "F fp32 | J W a g": ("", "", "2", "1", "1"),
+    "F fp32 | J Wfwd a g": ("", "", "f", "1", "1"),
+    "F fp32 | J Wbwd a g": ("", "", "b", "1", "1"),
+    "F fp32 | J w A G": ("", "", "1", "2", "2"),
+    "F fp32 | J W A g": ("", "", "2", "2", "1"),
     "F tc+edge5e-4 | J fp32": ("1", "1", "", "", "", "edge", 5e-4, "", ""),
     "F tc+band5e-4 | J fp32": ("1", "1", "", "", "", "band", 5e-4, "", ""),
     "F tc+edge5e-4(WA) | J tc": ("1", "1", "1", "1", "1", "edge", 5e-4, "2", "2"),

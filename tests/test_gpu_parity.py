@@ -4,8 +4,9 @@
   * the numpy oracle on seeded inputs (ragged sizes, empty inputs, failure paths),
   * size-independent properties at the BASELINE sizes (grid slabs vs whole grid, batching invariance).
 Tolerances (north_star): FP32 validation mode 1e-5 abs per SDF / Jacobian entry; tensor-core mode
-1e-3 abs for the SDF, Jacobian judged statistically (see DESIGN.md "precision"); per-GN-step pose
-within 1 cm / 0.1 deg and code within 1e-2.
+1e-3 abs for the SDF and for >= 95 % of the Jacobian rows (every entry of the row; the others are rows with a
+ReLU pre-activation within rounding of zero, see _jac_check); per-GN-step pose within 1 cm / 0.1 deg and code
+within 1e-2 - per object here, over the 160-object population in tests/test_gpu_parity_bulk.py.
 """
 import os
 
@@ -75,7 +76,8 @@ def _jac_check(mode, jac, ref):
         # pre-activation is within rounding of 0 flips and moves single entries by up to ~1e-1 (it does so between
         # any two FP32 implementations too, just more rarely).  Judge the distribution, not the max.
         assert np.sqrt((err ** 2).mean()) < 6e-4
-        assert (err.max(axis=1) <= 1e-3).mean() >= 0.90
+        assert (err.max(axis=1) <= 1e-3).mean() >= 0.95
+        assert (err <= 1e-3).mean() >= 0.998
         assert np.quantile(err, 0.999) < 4e-3
 
 
@@ -151,13 +153,15 @@ def _teacher_forced(eng, mode, g, cfg, steps, tol_H, tol_b):
     and next state.  FP32 mode: every step within the north_star tolerances.  Tensor-core mode: the Jacobian of a
     ReLU network is piecewise constant, and FP16-operand rounding flips a ReLU whose pre-activation is within ~1e-4
     of zero on a few percent of the rows; when such a row carries a large render coefficient one step can move H
-    by a few percent (seen: 1 step of 20).  So tensor-core mode asserts >= 90 % of the steps within the north_star
-    tolerances (the north_star asks for >= 95 % of OBJECTS within tolerance) and every step within loose bounds."""
+    by a few percent (seen: 1 step of 20).  The population statement (>= 95 % of 1 280 + 640 steps and of 160 objects
+    within the north_star tolerances) is asserted in tests/test_gpu_parity_bulk.py; with the 10 - 20 steps of ONE
+    object a single miss is already 5 - 10 %, so here tensor-core mode asserts at most 10 % misses at the same
+    tolerances as the FP32 mode and every step within loose bounds."""
     from dspslam import synth
     p = params(cfg, iters=1)
     n_it = g["H"].shape[0]
     strict_ok = []
-    code_tol = 1e-2 if mode == "fp32" else 3e-2      # see tests/golden/noise_floor.json for the reference's own spread
+    code_tol = 1e-2
     for e in steps:
         T_co = np.linalg.inv(g["T_oc"][e].astype(np.float64)).astype(np.float32)
         res = eng.gn_joint([(T_co, g["in_pts"], g["in_rays"], g["in_depth"], g["code_it"][e])], p, mode=mode, debug=True)

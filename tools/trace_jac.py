@@ -1,0 +1,64 @@
+"""Where does a layer step of the GN Jacobian kernel (k_tc<5>) spend its time?  Needs the trace build
+(`make -C dsp-slam-rgbd_b200/csrc trace`); runs one C2 batch and prints, for CTA 0 of the last Jacobian launch, the
+duration of every MMA phase (accumulator wait -> commit issued) and every epilogue (accumulator complete -> next A
+operand signalled) in SM cycles.   python tools/trace_jac.py [mode]"""
+import ctypes as C
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.abspath(os.path.join(os.path.dirname(__file__), ".."))
+sys.path[:0] = [os.path.join(ROOT, "dsp-slam-rgbd_b200"), ROOT]
+from dspslam import _native as N  # noqa: E402
+
+N.LIB_PATH = os.path.join(os.path.dirname(N.LIB_PATH), "libdspslam_sm100_trace.so")
+from dspslam import synth  # noqa: E402
+from reconstruct.optimizer import Optimizer  # noqa: E402
+
+mode = sys.argv[1] if len(sys.argv) > 1 else "tc"
+opt = Optimizer(synth.load_wfit(), synth.kitti_config(), mode=mode)
+eng = opt.engine
+dets = [synth.make_kitti_detection(k, M=2048, n_bg=200) for k in range(16)]
+batch = eng.upload_joint(eng.pack_joint(dets))
+for _ in range(2):
+    eng.run_joint(batch, opt._params())
+buf = (C.c_longlong * 8192)()
+eng.lib.dspslam_debug_trace.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+assert eng.lib.dspslam_debug_trace(eng._h, buf, 8192) == 0
+t = np.array(buf, dtype=np.int64)
+ne, nm = int(t[4095]), int(t[8191])
+E_ = t[:ne].reshape(-1, 2)
+M_ = t[4096:4096 + nm].reshape(-1, 2)
+t0 = min(E_[0, 0], M_[0, 0])
+print("mode %s: %d epilogue events, %d MMA events of CTA 0" % (mode, len(E_), len(M_)))
+# MMA phases: tag p*100+li = operands ready, 1000+... = commit issued (completion is seen by the epilogue's wait)
+print("-- first tile, per layer step: [MMA issue window] and [epilogue: accumulator complete -> signalled]")
+ev = sorted([(int(c - t0), "E", int(g)) for c, g in E_] + [(int(c - t0), "M", int(g)) for c, g in M_])
+last = {}
+rows = []
+for c, w, g in ev[:140]:
+    rows.append("%9d %s %5d" % (c, w, g))
+print("\n".join(rows))
+# summary over all tiles: epilogue durations by tag
+dur = {}
+start = {}
+for c, g in E_:
+    g = int(g)
+    if g < 1000:
+        start[g] = int(c)
+    elif g < 2000 and (g - 1000) in start:
+        dur.setdefault(g - 1000, []).append(int(c) - start[g - 1000])
+print("-- epilogue durations (cycles), median over tiles: tag 0-6 forward layers, 7 = g7 build, 101-107 backward")
+for g in sorted(dur):
+    print("  %4d: %7.0f" % (g, np.median(dur[g])))
+mstart, mdur = {}, {}
+for c, g in M_:
+    g = int(g)
+    if g < 1000:
+        mstart[g] = int(c)
+    elif (g - 1000) in mstart:
+        mdur.setdefault(g - 1000, []).append(int(c) - mstart[g - 1000])
+print("-- MMA issue windows (cycles; operands ready -> last MMA of the layer issued), median over tiles")
+for g in sorted(mdur):
+    print("  %4d: %7.0f" % (g, np.median(mdur[g])))
