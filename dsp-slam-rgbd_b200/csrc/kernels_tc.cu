@@ -41,7 +41,8 @@ constexpr int A_BYTES = 8 * A_BLK;
 constexpr int AX_BYTES = 4096;     // the K=16 extra block of the tile: 128 rows x 32 B, no swizzle
 constexpr int STAGE_BYTES = 16384;
 constexpr int JLD = 76;            // row stride (floats) of the per-row Jacobian buffer (float4-aligned rows)
-constexpr int PARK_LD = 68;        // row stride (floats) of the layer-4 input-gradient park in global memory
+constexpr int PARK_LD = 68;        // columns of the layer-4 input-gradient park in global memory, per CTA [PARK_LD][TILE_M]:
+                                   // column-major, so that the 32 rows of a warp store / load one 128-byte line
 constexpr int PARK_CTAS = 256;     // CTAs the park is sized for (grids are capped at the SM count)
 constexpr float GSCALE = 256.f;    // gradients are carried scaled so that FP16 keeps them normal
 constexpr int TMEM_COLS = 512;
@@ -182,7 +183,10 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     int n_tiles = a.n_tiles;
     if (C::GN) n_tiles = a.w.n_tiles[MODE == 3 ? 0 : 1];
     constexpr int NPROG = JAC ? 2 : 1;
-    const int nrep = (JAC && a.wsplit) ? 2 : 1;
+    // hi(W) + lo(W) passes in the FORWARD sweep only: the forward weights set the ReLU pattern and the SDF value the
+    // Jacobian hangs on; rounding the backward sweep's weights moves a GN step by nothing measurable
+    // (oracle/precision_study2.py: "J Wfwd a g" 98.8 % of steps = "J W a g"; "J Wbwd a g" 97.5 % = single pass)
+    const int nrep0 = (JAC && a.wsplit) ? 2 : 1;
     // tile walk: a pair takes tiles (tb, tb + 1); both CTAs make the same number of trips (the multicast protocol
     // needs them in step), a CTA whose tile index falls behind the list runs the trip with no valid rows
     const int rank = PAIR ? (int)(blockIdx.x & 1u) : 0;
@@ -196,6 +200,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             const int obj = C::GN ? a.w.tile_obj[t] : 0;
             const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
             for (int p = 0; p < NPROG; ++p) {
+                const int nrep = (p == 0) ? nrep0 : 1;
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
@@ -252,6 +257,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         };
         for (int tb = tb0; tb < n_tiles; tb += gridDim.x) {
             for (int p = 0; p < NPROG; ++p) {
+                const int nrep = (p == 0) ? nrep0 : 1;
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
@@ -310,7 +316,8 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         uint32_t mw[8][8];                                 // ReLU sign words of this thread's 256 columns, per layer
         const int L = a.dec.L;
         // layer-4 input gradients of row r wait here (written and read back by the hc == 1 thread of the row)
-        float* park = JAC ? a.dec.tc_park + ((size_t)blockIdx.x * TILE_M + r) * PARK_LD : nullptr;
+        float* park = JAC ? a.dec.tc_park + (size_t)blockIdx.x * TILE_M * PARK_LD + r : nullptr;
+#define PARK(c) park[(c) * TILE_M]
 
         auto signal_ready = [&]() {
             tc_fence_before();
@@ -505,24 +512,18 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                     TRACE_E(100 + l);
                     const bool split = (l == 4);             // columns >= h3 are d/d(input) (latent re-injection)
                     const int h3 = a.dec.h3, h3p = a.dec.h3p;
-#pragma unroll 1
-                    for (int j = 0; j < 8; ++j) {
-                        const int col = hc * 256 + j * 32;
-                        uint32_t v[32];
-                        tmem_ld32(trow + col, v);
-                        tmem_ld_wait();
-                        const uint32_t m = mw[l - 1][j];
+                    // one 32-column group: mask with relu'(a_{l-1}), park the input-gradient columns of layer 4, store
+                    auto group = [&](int col, uint32_t (&v)[32], uint32_t m) {
                         if (split && col >= h3p) {           // pure input-gradient columns
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) park[col + i - h3] = __uint_as_float(v[i]);
-                            continue;
+                            for (int i = 0; i < 32; ++i) PARK(col + i - h3) = __uint_as_float(v[i]);
+                            return;
                         }
-                        uint32_t p[16];
                         if (split && col + 32 > h3) {        // the group that straddles h3 (445)
 #pragma unroll
                             for (int i = 0; i < 32; ++i) {
                                 const bool hid = (col + i) < h3;
-                                if (!hid) park[col + i - h3] = __uint_as_float(v[i]);
+                                if (!hid) PARK(col + i - h3) = __uint_as_float(v[i]);
                                 if (!hid || !((m << i) & 0x80000000u)) v[i] = 0u;
                             }
                         } else {
@@ -530,10 +531,21 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                             for (int i = 0; i < 32; ++i)
                                 if (!((m << i) & 0x80000000u)) v[i] = 0u;
                         }
+                        uint32_t p[16];
 #pragma unroll
                         for (int i = 0; i < 16; ++i)
                             p[i] = pack_f16x2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
                         store32(col, p);
+                    };
+#pragma unroll 1
+                    for (int jp = 0; jp < 4; ++jp) {         // two TMEM loads in flight per wait, like the forward sweep
+                        const int col = hc * 256 + jp * 64;
+                        uint32_t v0[32], v1[32];
+                        tmem_ld32(trow + col, v0);
+                        tmem_ld32(trow + col + 32, v1);
+                        tmem_ld_wait();
+                        group(col, v0, mw[l - 1][2 * jp]);
+                        group(col + 32, v1, mw[l - 1][2 * jp + 1]);
                     }
                     signal_ready();
                     TRACE_E(1100 + l);
@@ -545,40 +557,49 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                 tc_fence_after();
                 TRACE_E(100);
                 const float inv_s = 1.f / GSCALE;
-                if (hc == 1) {                                // the thread that parked the row's layer-4 gradients
-                    uint32_t v0[32], v1[32], v2[32];
-                    tmem_ld32(trow + 0, v0);
-                    tmem_ld32(trow + 32, v1);
-                    tmem_ld32(trow + 64, v2);
-                    tmem_ld_wait();
+                // The two threads of a row share the <= 96 columns: hc == 0 takes columns 0-31 (when the code is at least
+                // 32 long), hc == 1 the rest, including the three xyz columns and (GN) the pose part of the J row.
+                {
+                    const bool lo_half = (L >= 32);          // (uniform) columns 0-31 are code columns owned by hc == 0
                     float* jr = jrow + r * JLD;
-                    if (MODE == 4) {
+                    const float cf = (MODE == 5) ? xyzs[r].w : 1.f;
+                    const int o = (MODE == 5) ? POSE : 0;    // MODE 4 rows are [code | xyz], GN rows [pose 7 | code]
+                    if (hc == 0) {
+                        if (lo_half) {
+                            uint32_t v0[32];
+                            tmem_ld32(trow + 0, v0);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            if (i < L + 3) jr[i] = (__uint_as_float(v0[i]) + park[i]) * inv_s;
-                            if (32 + i < L + 3) jr[32 + i] = (__uint_as_float(v1[i]) + park[32 + i]) * inv_s;
-                            if (64 + i < L + 3) jr[64 + i] = (__uint_as_float(v2[i]) + park[64 + i]) * inv_s;
+                            for (int i = 0; i < 32; ++i) jr[o + i] = cf * (__uint_as_float(v0[i]) + PARK(i)) * inv_s;
                         }
                     } else {
-                        // J row = [pose 7 | code L]
-                        auto dval = [&](int i) -> float {
-                            return __uint_as_float(i < 32 ? v0[i & 31] : (i < 64 ? v1[i & 31] : v2[i & 31]));
+                        uint32_t v0[32], v1[32], v2[32];
+                        if (!lo_half) tmem_ld32(trow + 0, v0);
+                        tmem_ld32(trow + 32, v1);
+                        tmem_ld32(trow + 64, v2);
+                        tmem_ld_wait();
+                        float gxyz[3] = {0.f, 0.f, 0.f};
+                        auto col_out = [&](int i, float d) {      // column i of D: a code column or one of the xyz columns
+                            const float g = (d + PARK(i)) * inv_s;
+                            if (i < L) jr[o + i] = cf * g;
+                            else if (i < L + 3) {
+                                if (MODE == 4) jr[i] = g;
+                                else gxyz[i - L] = g;
+                            }
                         };
-                        float gxyz[3];
+                        if (!lo_half) {
 #pragma unroll
-                        for (int c = 0; c < 3; ++c) gxyz[c] = 0.f;
-#pragma unroll
-                        for (int i = 0; i < 96; ++i) {
-                            if (i >= L && i < L + 3) gxyz[i - L] = (dval(i) + park[i]) * inv_s;
+                            for (int i = 0; i < 32; ++i) if (i < L + 3) col_out(i, __uint_as_float(v0[i]));
                         }
-                        const float4 pc = xyzs[r];
-                        const float cf = pc.w;
 #pragma unroll
-                        for (int i = 95; i >= 0; --i) {
-                            if (i < L) jr[POSE + i] = cf * (dval(i) + park[i]) * inv_s;
+                        for (int i = 0; i < 32; ++i) if (32 + i < L + 3) col_out(32 + i, __uint_as_float(v1[i]));
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) if (64 + i < L + 3) col_out(64 + i, __uint_as_float(v2[i]));
+                        if (MODE == 5) {
+                            const float4 pc = xyzs[r];
+                            build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
+                            for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;    // padding columns of the 4x4 blocks
                         }
-                        build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
-                        for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;    // padding columns of the 4x4 blocks
                     }
                 }
                 tc_fence_before();

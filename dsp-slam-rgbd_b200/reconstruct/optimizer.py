@@ -56,6 +56,10 @@ def _resolve_engine(decoder=None, configs=None):
     eng = _last_engine() if _last_engine is not None else None
     if eng is not None and getattr(eng, "_h", None):
         return eng
+    from dspslam.engine import last_engine
+    eng = last_engine()
+    if eng is not None:
+        return eng
     if configs is None:
         raise ValueError("no decoder, no configs and no live engine to borrow")
     from reconstruct.utils import get_decoder

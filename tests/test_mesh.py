@@ -205,8 +205,9 @@ def test_c4_grid_mesh_vertex_set_volume_area(eng):
         want = crossing_set(h)
         assert v.shape == want.shape
         from scipy.spatial import cKDTree
-        dist, idx = cKDTree(want).query(v)                 # one-to-one match within FP32 rounding of the interpolation
-        assert dist.max() < 4e-6 and np.unique(idx).size == v.shape[0]
+        # same count, and every vertex of either set has a partner in the other within FP32 rounding of the
+        # interpolation (not asserted one-to-one: a level crossing exactly at a grid node is emitted by two edges)
+        assert cKDTree(want).query(v)[0].max() < 4e-6 and cKDTree(v).query(want)[0].max() < 4e-6
         assert mc_oracle.mesh_topology(f)[:3] == (0, 0, 0)
         vol, area = mesh_volume_area(v, f)
         vox = float((h < 0).sum()) * (2.0 / (G - 1)) ** 3
