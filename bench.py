@@ -60,6 +60,19 @@ def make_dets(rank, n=OBJ_PER_RANK):
     return [synth.make_kitti_detection(rank * OBJ_PER_RANK + k, M=M_PTS, n_bg=N_BG) for k in range(n)]
 
 
+def traffic_of(kernel):
+    """dram bytes per launch of `kernel` from the committed ncu capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
+            k = json.load(f)["kernels"]
+        for name, v in k.items():
+            if kernel in name:
+                return int(v["traffic_bytes"])
+    except (OSError, KeyError, ValueError):
+        pass
+    return None
+
+
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.isfile(path):
@@ -318,11 +331,11 @@ def ours_arm(args, rank, world, local_rank):
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": "forward-only decoder over in-ball ray samples (GN render term)",
                      "achieved": fwd_tf, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": fwd_tf / pk["tflops"],
-                     # DRAM bytes of one forward launch (read + write) from the committed `ncu --set full` capture of
-                     # this command: profiles/r01_ncu_full_bench_k_tc_pair_summary.txt (weights + 16 B per sample in,
-                     # 4 B out; activations never leave the SM)
-                     "traffic": (16552960 + 0) if args.mode == "tc" else None,
-                     "traffic_source": "profiles/r01_ncu_full_bench_k_tc_pair_summary.txt (dram__bytes_read+write.sum)",
+                     # DRAM bytes of one forward launch (read + write) from the committed `ncu --set full` capture of this
+                     # command (tools/ncu_traffic.py -> profiles/r02_traffic.json); null when the file is missing
+                     "traffic": traffic_of("k_tc<3>") if args.mode != "fp32" else None,
+                     "traffic_source": "profiles/r02_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum, "
+                                       "profiles/r02_prof_bench_k_tc.ncu-rep)",
                      "peak_source": pk["src"],
                      "avg_launch_ms": prof["ms_gn_fwd"] / max(1, prof["n_gn_fwd"]),
                      "rows_per_launch": prof["rows_gn_fwd"] / max(1, prof["n_gn_fwd"]),

@@ -18,14 +18,17 @@ _MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE
           "mix_fwd_tc": 2, "mix_jac_tc": 3}     # diagnostic mixes (tools/free_run_stats.py)
 
 
-_LAST = None      # weak reference to the engine constructed last in this process
+_LIVE = []        # weak references to the engines constructed in this process, oldest first
 
 
 def last_engine():
-    """The most recently constructed live Engine of the process, or None (callers that are handed neither a decoder
-    nor a config - `convert_sdf_voxels_to_mesh`, the sequence classes - borrow it)."""
-    eng = _LAST() if _LAST is not None else None
-    return eng if (eng is not None and getattr(eng, "_h", None)) else None
+    """The most recently constructed Engine of the process that is still alive, or None (callers that are handed
+    neither a decoder nor a config - `convert_sdf_voxels_to_mesh`, the sequence classes - borrow it)."""
+    for ref in reversed(_LIVE):
+        eng = ref()
+        if eng is not None and getattr(eng, "_h", None):
+            return eng
+    return None
 
 
 def _align(n, a=256):
@@ -80,8 +83,7 @@ class Engine:
         self._keep = layers
         self._pinned = {}
         import weakref
-        global _LAST
-        _LAST = weakref.ref(self)
+        _LIVE[:] = [r for r in _LIVE if r() is not None] + [weakref.ref(self)]
         if self.mode != N.MODE_FP32 and not self.lib.dspslam_mode_available(h, N.MODE_TC):
             why = (self.lib.dspslam_last_error() or b"").decode()
             self.close()

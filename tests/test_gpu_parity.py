@@ -168,7 +168,9 @@ def _teacher_forced(eng, mode, g, cfg, steps, tol_H, tol_b):
         d = res.dbg[0, 0]
         H, b = d[:5041].reshape(71, 71), d[5041:5112]
         assert res.status[0] == 0
-        assert abs(int(d[5112]) - int(g["K"][e])) <= (2 if mode == "fp32" else 12), (e, d[5112], g["K"][e])
+        # the reference's own row count moves by 1-2 rows in ~400 between 1 and 8 CPU threads
+        Kref = int(g["K"][e])
+        assert abs(int(d[5112]) - Kref) <= (max(2, Kref // 300) if mode == "fp32" else max(4, Kref // 100)), (e, d[5112], Kref)
         eH = np.linalg.norm(H - g["H"][e]) / np.linalg.norm(g["H"][e])
         eb = np.linalg.norm(b - g["b"][e]) / np.linalg.norm(g["b"][e])
         Tn, cn = ((np.linalg.inv(g["T_oc"][e + 1].astype(np.float64)), g["code_it"][e + 1]) if e + 1 < n_it
@@ -354,6 +356,31 @@ def test_c2_sized_object_fp32_vs_oracle(eng, odec):
     assert np.linalg.norm(b - trace[0]["b"]) / np.linalg.norm(trace[0]["b"]) < 1e-3
     dt, ang, _ = synth.pose_errors(res.t_cam_obj[0], o["t_cam_obj"])
     assert dt < 1e-3 and ang < 1e-2
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("k", [0, 1, 2, 3])
+def test_c2_sized_gn_steps_vs_reference(mode, k, eng):
+    """BASELINE C2 size against the reference itself: M = 2048 surface points, 2248 rays x 50 samples, ~2.5 k render
+    rows per iteration; per-iteration state, H, b and K from the unmodified reference (oracle/make_goldens_bulk.py,
+    ~10 s per object on CPU).  The inputs are regenerated from the seed and checked against the stored checksum."""
+    from dspslam import synth
+    g = load("c2_obj%d.npz" % k)
+    det = synth.make_kitti_detection(k, M=2048, n_bg=200)
+    chk = float(sum(np.asarray(det[n], np.float64).sum() for n in ("t_cam_obj", "pts", "rays", "depth")))
+    assert abs(chk - float(g["in_sum"])) < 1e-6 * max(1.0, abs(chk))
+    g.update(in_pts=det["pts"], in_rays=det["rays"], in_depth=det["depth"])
+    tol = (3e-3, 1e-2) if mode == "fp32" else (3e-2, 6e-2)
+    _teacher_forced(eng, mode, g, synth.kitti_config(), range(10), *tol)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_grid_g64_vs_reference_golden(mode, eng):
+    """MeshExtractor's grid (optimizer.py:224-228) at G = 64 for an optimised code, from the reference's own
+    `decode_sdf` over its sheared `create_voxel_grid`."""
+    g = load("grid_sdf_g64.npz")
+    out = eng.grid_sdf(g["code"], 64, mode=mode).cpu().numpy().reshape(64, 64, 64)
+    assert np.abs(out - g["sdf"]).max() < TOL_SDF[mode]
 
 
 def test_grid_sharded_equals_single(eng):
