@@ -41,12 +41,15 @@ class EmuDecoder(orc.OracleDecoder):
         super().__init__(sd)
         self.spec = spec
         need = set((spec[0], spec[2]) + ((spec[7],) if len(spec) > 5 else ()))
-        if need & {"f", "b"}:
-            need = (need - {"f", "b"}) | {"1", "2"}
+        if need & {"f", "b", "lo3", "hi4"}:
+            need = (need - {"f", "b", "lo3", "hi4"}) | {"1", "2"}
         self.Wv = {m: [RND[m](w) for w in self.W] for m in need}
 
     def _fwd(self, inp, wm, am, keep):
-        W = self.Wv[wm]
+        if wm in ("lo3", "hi4"):      # hi+lo weights in layers 1-3 / 4-7 only
+            W = [self.Wv["2"][k] if ((k <= 3) == (wm == "lo3")) else self.Wv["1"][k] for k in range(self.n_layers)]
+        else:
+            W = self.Wv[wm]
         h = inp
         acts = []
         nl = self.n_layers
@@ -91,7 +94,7 @@ class EmuDecoder(orc.OracleDecoder):
         inp = np.concatenate([np.broadcast_to(code, (x.shape[0], code.shape[0])), x], axis=-1)
         jw = self.spec[2]
         out, acts = self._fwd(inp, "1" if jw == "b" else ("2" if jw == "f" else jw), self.spec[3], True)
-        W = self.Wv["2" if jw == "b" else ("1" if jw == "f" else jw)]      # 'f' / 'b': hi+lo weights in the forward / backward sweep only
+        W = self.Wv["2" if jw == "b" else ("1" if jw in ("f", "lo3", "hi4") else jw)]      # 'f' / 'b': hi+lo weights in the forward / backward sweep only
         gm = RND[self.spec[4]]
         g = (1 - out * out).astype(np.float32) @ self.W[self.n_layers - 1]
         g_in = 0
@@ -117,6 +120,8 @@ VARIANTS = {
     "F W a | J W A G": ("2", "1", "2", "2", "2"),
     "F fp32 | J W a g": ("", "", "2", "1", "1"),
     "F fp32 | J Wfwd a g": ("", "", "f", "1", "1"),
+    "F fp32 | J Wfwd(1-3) a g": ("", "", "lo3", "1", "1"),
+    "F fp32 | J Wfwd(4-7) a g": ("", "", "hi4", "1", "1"),
     "F fp32 | J Wbwd a g": ("", "", "b", "1", "1"),
     "F fp32 | J w A G": ("", "", "1", "2", "2"),
     "F fp32 | J W A g": ("", "", "2", "2", "1"),
