@@ -119,8 +119,9 @@ class ClockSampler:
         sm = sorted(float(r[0]) for r in rows)
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
+        pw = [float(r[2]) for r in rows]
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
-                "samples": len(rows), "power_w_max": max(float(r[2]) for r in rows)}
+                "samples": len(rows), "power_w_max": max(pw), "power_w_mean": float(np.mean(pw))}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -359,6 +360,10 @@ def ours_arm(args, rank, world, local_rank):
                    "note": "ray samples within refine_window * cut_off of a decision threshold, evaluated a second "
                            "time with hi+lo FP16 operand pairs (k_tc_refine) before the per-ray scan"},
     }
+    if clocks and clocks.get("power_w_mean"):
+        # energy per object on rank 0's board while the timed steps ran (nvidia-smi power.draw, 100 ms samples; the
+        # region also holds the untimed L2 flushes, so this is a lower bound on objects per joule)
+        line["objects_per_joule"] = (value / world) / clocks["power_w_mean"]
     line.update(extra)
     if world == 1 and not args.no_cpu:
         secs, thr, kind = cpu_sample(2, warm=1)
@@ -398,6 +403,25 @@ def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ran
     if args.skip_configs:
         return out
     eng = opt.engine
+    # ---- the other tensor-core operating points on the same resident batch (rank 0; objects/s per GPU) ----
+    if rank == 0:
+        prm0 = opt._params()
+        batch0 = eng.upload_joint(eng.pack_joint(make_dets(rank)))
+        modes = {}
+        for m in ("tc_fast", "tc", "tc_exact"):
+            for _ in range(2):
+                eng.run_joint(batch0, prm0, mode=m)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            torch.cuda.synchronize()
+            ev[0].record()
+            for _ in range(3):
+                eng.run_joint(batch0, prm0, mode=m)
+            ev[1].record()
+            torch.cuda.synchronize()
+            modes[m] = OBJ_PER_RANK * 3 / (ev[0].elapsed_time(ev[1]) * 1e-3)
+        out["modes_objects_per_s_per_gpu"] = dict(modes, note="C2 batch resident, 3 steps each, no L2 flush; parity of "
+                                                  "each mode: profiles/r02_parity_*.jsonl, tests/test_gpu_parity_bulk.py")
+        del batch0
     # ---- C1 latency ----
     if rank == 0:
         d = synth.make_kitti_detection(0)
@@ -480,7 +504,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--mode", default="tc", choices=["tc", "tc_fast", "fp32"])
+    ap.add_argument("--mode", default="tc", choices=["tc", "tc_fast", "tc_exact", "fp32"])
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--skip-configs", action="store_true", help="skip the c1 / c4 / c5 / parity legs")
     ap.add_argument("--ray-phases", type=int, default=0,

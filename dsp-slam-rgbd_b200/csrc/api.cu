@@ -1,6 +1,7 @@
 // C ABI of libdspslam_sm100 (include/dspslam.h): handle, weight packing, workspace,
 // and the launch sequences of the Gauss-Newton drivers.  No exception crosses the ABI.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -40,6 +41,10 @@ struct dspslam_handle {
     int32_t* zeros = nullptr;    // zero offsets for the ray-less pose-only driver
     size_t zeros_cap = 0;
     int64_t launches = 0;
+    int wsplit_mask = 0xF0;      // layers whose forward-sweep weights the Jacobian kernel takes as hi + lo pairs: 4-7
+                                 // (measured on 1 280 reference steps: 4-7 97.4 % within tolerance at 488 objects/s,
+                                 // 1-7 96.9 % at 477, 5-7 95.9 % at 491, 1-3 96.2 % at 491, none 95.9 % at 500;
+                                 // experiment knob: environment variable DSPSLAM_WSPLIT_MASK at handle creation)
     bool tc_ready = false;
     std::string tc_why;          // why the tcgen05 path is unavailable for this decoder
     std::mutex mu;
@@ -218,7 +223,7 @@ int64_t dspslam_launch_count(const dspslam_handle* h) { return h ? h->launches :
 int dspslam_mode_available(const dspslam_handle* h, int mode) {
     if (!h) { g_err = "null handle"; return 0; }
     if (mode == DSPSLAM_MODE_FP32) return 1;
-    if (mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) { g_err = "unknown mode"; return 0; }
+    if (mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST && mode != DSPSLAM_MODE_TC_EXACT) { g_err = "unknown mode"; return 0; }
     if (!h->tc_ready) { g_err = h->tc_why; return 0; }
     return 1;
 }
@@ -265,6 +270,7 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
+    if (const char* m = getenv("DSPSLAM_WSPLIT_MASK")) h->wsplit_mask = (int)strtol(m, nullptr, 0) & 0xFE;
     if (rc == 1) h->tc_why = tc_last_error();
     *out = h;
     return 0;
@@ -290,7 +296,8 @@ void dspslam_destroy(dspslam_handle* h) {
 static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz, int64_t n,
                    float* sdf_out, float* jac_out) {
     if (!h || n < 0) return fail(DSPSLAM_E_BADARG, "null/negative argument");
-    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST && mode != DSPSLAM_MODE_TC_EXACT)
+        return fail(DSPSLAM_E_BADARG, "bad mode");
     if (n == 0) return 0;                       // empty query: nothing to do (pointers may be null)
     if (!code || !xyz || !sdf_out) return fail(DSPSLAM_E_BADARG, "null argument");
     if (n > ((int64_t)1 << 31) - 256) return fail(DSPSLAM_E_BADARG, "n too large for one call");
@@ -305,8 +312,10 @@ static int run_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
         else launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, sdf_out, S(stream));
         ++nl;
     } else {
-        if (jac_out) nl += tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out,
-                                             mode == DSPSLAM_MODE_TC ? 1 : 0, S(stream));
+        if (jac_out && mode == DSPSLAM_MODE_TC_EXACT)
+            nl += tc_launch_sdf_jac_exact(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out, S(stream));
+        else if (jac_out) nl += tc_launch_sdf_jac(h->dec, h->sm_count, xyz, n, c0, c4, sdf_out, jac_out,
+                                                  mode == DSPSLAM_MODE_TC ? h->wsplit_mask : 0, S(stream));
         else nl += tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, sdf_out, S(stream));
     }
     prof_end(h, pp, S(stream));
@@ -354,7 +363,8 @@ int dspslam_grid_sdf(dspslam_handle* h, void* stream, int mode, const float* cod
     if (i0 < 0 || i1 < i0 || i1 > total) return fail(DSPSLAM_E_BADARG, "bad index range");
     if (coord_mode != DSPSLAM_GRID_REFERENCE_SHEAR && coord_mode != DSPSLAM_GRID_LATTICE)
         return fail(DSPSLAM_E_BADARG, "bad coord_mode");
-    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST && mode != DSPSLAM_MODE_TC_EXACT)
+        return fail(DSPSLAM_E_BADARG, "bad mode");
     if (i1 == i0) return 0;
     if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
     std::lock_guard<std::mutex> lk(h->mu);
@@ -395,10 +405,11 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
                   int max_rays, const float* pose_in, float* pose_out, const float* code_in, float* code_out,
                   const float* scale_in, int32_t* status_out, float* loss_out, float* dbg_out, int dbg_stride) {
     // diagnostic mixes (not in the public header): 2 = tensor-core forward samples + FP32 Jacobian rows, 3 = the reverse
-    if (mode < 0 || mode > 4) return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode < 0 || mode > 5) return fail(DSPSLAM_E_BADARG, "bad mode");
     if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
-    const bool fast = (mode == DSPSLAM_MODE_TC_FAST);
-    const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2 || fast), jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3 || fast);
+    const bool fast = (mode == DSPSLAM_MODE_TC_FAST), exact = (mode == DSPSLAM_MODE_TC_EXACT);
+    const bool fwd_tc = (mode == DSPSLAM_MODE_TC || mode == 2 || fast || exact);
+    const bool jac_tc = (mode == DSPSLAM_MODE_TC || mode == 3 || fast || exact);
     if (B <= 0 || B > 65535) return fail(DSPSLAM_E_BADARG, "B must be in 1..65535");
     if (iters < 0) return fail(DSPSLAM_E_BADARG, "negative iteration count");
     const int D = prm.D;
@@ -414,7 +425,8 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.total_rays = (int)total_rays;
     w.total_pts = (int)total_pts;
     w.fgroups_max = (int)(((int64_t)max_rays * D + GROUP_ROWS - 1) / GROUP_ROWS);
-    w.jgroups_max = (int)(((int64_t)max_pts + (int64_t)max_rays * D + GROUP_ROWS - 1) / GROUP_ROWS);
+    w.jac_rows = exact ? REFINE_ROWS : GROUP_ROWS;
+    w.jgroups_max = (int)(((int64_t)max_pts + (int64_t)max_rays * D + w.jac_rows - 1) / w.jac_rows);
     if (w.jgroups_max < 1) w.jgroups_max = 1;
     w.pts_off = pts_off; w.ray_off = ray_off; w.n_fg = n_fg;
     w.pts = pts; w.rays = rays; w.depth = depth;
@@ -427,7 +439,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
 
     // second, FP32-grade evaluation of the ray samples next to a decision threshold (tensor-core forward pass only)
     const bool refine = fwd_tc && !fast && !prm.pose_only && refine_window >= 0.f;
-    w.jac_wsplit = (jac_tc && !fast) ? 1 : 0;
+    w.jac_wsplit = (jac_tc && !fast) ? h->wsplit_mask : 0;
     w.refine_eps = refine ? (refine_window > 0.f ? refine_window : 0.05f) * prm.th : 0.f;
     const size_t rgroups_max = refine ? (size_t)(((int64_t)max_rays * D + REFINE_ROWS - 1) / REFINE_ROWS) : 0;
     size_t max_tiles = (size_t)B * (size_t)(w.jgroups_max > w.fgroups_max ? w.jgroups_max : w.fgroups_max) + 1;
@@ -520,6 +532,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
         }
         const int pj = prof_begin(h, PK_GN_JAC, 0, st);
         if (!jac_tc) { launch_gn_jac_simt(w, st); ++nl; }
+        else if (exact) nl += tc_launch_gn_jac_exact(w, h->sm_count, st);
         else nl += tc_launch_gn_jac(w, h->sm_count, st);
         prof_end(h, pj, st);
         launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); ++nl;

@@ -59,7 +59,7 @@ static __device__ void plan_tiles(const GnWork& w, int which) {
     __shared__ int s_carry;
     __shared__ int s_off[1025];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
-    const int TR = (which == 2) ? REFINE_ROWS : GROUP_ROWS;      // rows per tile
+    const int TR = (which == 2) ? REFINE_ROWS : (which == 1 ? w.jac_rows : GROUP_ROWS);      // rows per tile
     if (tid == 0) s_carry = 0;
     __syncthreads();
     for (int base = 0; base < w.B; base += blockDim.x) {

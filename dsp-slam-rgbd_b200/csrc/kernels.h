@@ -10,7 +10,8 @@ struct GnWork {
     JointParamsDev prm;
     int B;
     int total_rays, total_pts;
-    int jgroups_max;   // 128-row groups per object in the Jacobian kernel grid / partial slots per object
+    int jac_rows;      // rows per Jacobian tile / partial slot: GROUP_ROWS (128), or REFINE_ROWS (64) in the exact mode
+    int jgroups_max;   // jac_rows-row groups per object in the Jacobian kernel grid / partial slots per object
     int fgroups_max;   // 128-row groups per object in the forward (ray-sample) kernel grid
     int n_phases;      // front-to-back ray phases per iteration (1: every in-ball sample in one pass)
     int phase;         // phase the sample / forward launches of this view work on

@@ -680,7 +680,7 @@ __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int l
             atomicAdd(w.stats + 1, (unsigned long long)(s.M_active + K));
             atomicAdd(w.stats + 2, (unsigned long long)(w.prm.pose_only ? 0 : s.n_valid));
         }
-        const int ng = (M + K + GROUP_ROWS - 1) / GROUP_ROWS;
+        const int ng = (M + K + w.jac_rows - 1) / w.jac_rows;
         const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
         for (int e = tid; e < n * n + n; e += SOLVE_NT) {
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;

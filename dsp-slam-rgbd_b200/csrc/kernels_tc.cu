@@ -74,7 +74,8 @@ struct TcArgs {
     float* out;
     float* jac_out;
     int n_tiles;
-    int wsplit;              // 1: every hidden K chunk is issued against hi(W) and lo(W) (Jacobian variants of DSPSLAM_MODE_TC)
+    int wsplit;              // bit l set: the forward sweep of the Jacobian variants issues every hidden K chunk of layer l
+                             // against hi(W) and lo(W) (DSPSLAM_MODE_TC)
     // Gauss-Newton work lists
     GnWork w;
 };
@@ -186,7 +187,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
     // hi(W) + lo(W) passes in the FORWARD sweep only: the forward weights set the ReLU pattern and the SDF value the
     // Jacobian hangs on; rounding the backward sweep's weights moves a GN step by nothing measurable
     // (oracle/precision_study2.py: "J Wfwd a g" 98.8 % of steps = "J W a g"; "J Wbwd a g" 97.5 % = single pass)
-    const int nrep0 = (JAC && a.wsplit) ? 2 : 1;
+    const int wsplit = JAC ? a.wsplit : 0;
     // tile walk: a pair takes tiles (tb, tb + 1); both CTAs make the same number of trips (the multicast protocol
     // needs them in step), a CTA whose tile index falls behind the list runs the trip with no valid rows
     const int rank = PAIR ? (int)(blockIdx.x & 1u) : 0;
@@ -200,9 +201,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
             const int obj = C::GN ? a.w.tile_obj[t] : 0;
             const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
             for (int p = 0; p < NPROG; ++p) {
-                const int nrep = (p == 0) ? nrep0 : 1;
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
+                    const int nrep = (p == 0 && ((wsplit >> li) & 1)) ? 2 : 1;
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
                     if (ld.xkind) {                              // the K=16 extra block (bias / latent / xyz)
                         mbar_wait(bar_empty(s), ph ^ 1u);
@@ -257,9 +258,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         };
         for (int tb = tb0; tb < n_tiles; tb += gridDim.x) {
             for (int p = 0; p < NPROG; ++p) {
-                const int nrep = (p == 0) ? nrep0 : 1;
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
+                    const int nrep = (p == 0 && ((wsplit >> li) & 1)) ? 2 : 1;
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
                     mbar_wait(bar_aready, aph);                  // this layer's A operand written, accumulator drained
                     aph ^= 1u;
@@ -1013,6 +1014,531 @@ __global__ void __launch_bounds__(NT, 1) k_tc_refine(const __grid_constant__ TcA
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_tc_jacx: SDF + Jacobian at FP32 grade on the tensor cores (DSPSLAM_MODE_TC_EXACT).
+//
+// The stacked hi/lo scheme of k_tc_refine carried through BOTH sweeps: a tile holds 64 real rows, tile row r is the hi
+// half and row r + 64 the lo half of the row's A operand (activations in the forward sweep, input gradients in the
+// backward sweep), every K chunk is issued against the hi(W) and the lo(W) stage image, and the epilogue warps q and
+// q + 2 add the two TMEM lane halves by swapping 32-column slices through shared memory.  The thread that finalises a
+// column keeps its ReLU sign bit and applies it to the same column of the backward sweep (the columns of D_l = g_l W_l
+// are the units of layer l - 1, so the ownership is the same in both directions).
+//   GN = false: rows from an xyz array -> sdf[n], jac[n][L + 3]          (dspslam_sdf_jac)
+//   GN = true : rows from the Jacobian work list (64-row tiles) -> per-tile J^T J | J^T r partials (dspslam_gn_*)
+// Cost: 4 single-pass rows of tensor work per real row and a heavier epilogue - about 4x the FP16 kernel per row.
+// ------------------------------------------------------------------------------------------------
+struct XCfg {
+    static constexpr int NST = 3;
+    static constexpr int ROWS = REFINE_ROWS;                        // real rows per tile
+    static constexpr int O_AX = A_BYTES;
+    static constexpr int O_ST = O_AX + AX_BYTES;
+    static constexpr int XB_WARP = 32 * 32 * 4;
+    static constexpr int O_XB = O_ST + NST * STAGE_BYTES;
+    static constexpr int O_W8 = O_XB + 8 * XB_WARP;
+    static constexpr int O_XYZ = O_W8 + 2048;                       // float4 x 64
+    static constexpr int O_PART = O_XYZ + 1024;                     // 4 x 64 floats
+    static constexpr int O_WROW = O_PART + 1024;                    // 64 floats
+    static constexpr int O_RT = O_WROW + 256;                       // 64 floats
+    static constexpr int O_BAR = O_RT + 256;
+    static constexpr int SMEM = O_BAR + 256 + 1024;
+};
+static_assert(XCfg::ROWS * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the activation tile");
+
+template <bool GN>
+__global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArgs a) {
+    using C = XCfg;
+    constexpr int NST = C::NST;
+    constexpr int ROWS = C::ROWS;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t raw = smem_u32(smem_raw);
+    const uint32_t sbase = (raw + 1023u) & ~1023u;
+    uint8_t* sm = smem_raw + (sbase - raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t sA = sbase, sAX = sbase + C::O_AX, sST = sbase + C::O_ST;
+    float* w8s = reinterpret_cast<float*>(sm + C::O_W8);
+    float4* xyzs = reinterpret_cast<float4*>(sm + C::O_XYZ);
+    float* parts = reinterpret_cast<float*>(sm + C::O_PART);
+    float* wrows = reinterpret_cast<float*>(sm + C::O_WROW);
+    float* rts = reinterpret_cast<float*>(sm + C::O_RT);
+    float* jrow = reinterpret_cast<float*>(sm);
+    const uint32_t bar0 = sbase + C::O_BAR;
+    auto bar_full = [&](int s) { return bar0 + 8u * s; };
+    auto bar_empty = [&](int s) { return bar0 + 8u * (NST + s); };
+    const uint32_t bar_aready = bar0 + 8u * (2 * NST), bar_dfull = bar0 + 8u * (2 * NST + 1);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + C::O_BAR + 8 * (2 * NST + 2));
+
+    if (tid == 0) {
+        for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
+        mbar_init(bar_aready, 8);
+        mbar_init(bar_dfull, 1);
+        fence_mbar_init();
+    }
+    if (warp == 9) {
+        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
+        tmem_relinquish();
+    }
+    for (int i = tid; i < HID; i += NT) w8s[i] = __ldg(a.dec.w8 + i);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = *tmem_slot;
+    const int n_tiles = GN ? a.w.n_tiles[1] : a.n_tiles;
+
+    if (warp == 8) {
+        // ===================== weight producer: both programs, every K chunk as a hi(W) and a lo(W) stage =====================
+        uint32_t s = 0, ph = 0;
+        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
+            const int obj = GN ? a.w.tile_obj[tb] : 0;
+            const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
+            for (int p = 0; p < 2; ++p) {
+#pragma unroll 1
+                for (int li = 0; li < 8; ++li) {
+                    const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
+                    if (ld.xkind) {
+                        mbar_wait(bar_empty(s), ph ^ 1u);
+                        if (elect_one()) {
+                            const uint32_t bytes = (uint32_t)ld.n * 32u;
+                            mbar_expect_tx(bar_full(s), bytes);
+                            bulk_g2s(sST + s * STAGE_BYTES, (ld.xkind == 2 ? xo : a.blob) + ld.xsrc, bytes, bar_full(s));
+                        }
+                        __syncwarp();
+                        if (++s == NST) { s = 0; ph ^= 1u; }
+                    }
+                    const uint8_t* src_hi = a.blob + ld.src;
+                    const uint8_t* src_lo = a.blob + ld.src_lo;
+                    for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                        const uint32_t bytes = (uint32_t)min(256, (int)ld.n - n0) * 64u;
+#pragma unroll 1
+                        for (int k2 = 0; k2 < 2 * ld.k32; ++k2) {
+                            mbar_wait(bar_empty(s), ph ^ 1u);
+                            if (elect_one()) {
+                                mbar_expect_tx(bar_full(s), bytes);
+                                bulk_g2s(sST + s * STAGE_BYTES, (k2 & 1) ? src_lo : src_hi, bytes, bar_full(s));
+                            }
+                            __syncwarp();
+                            if (k2 & 1) { src_hi += bytes; src_lo += bytes; }
+                            if (++s == NST) { s = 0; ph ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 9) {
+        // ===================== MMA issuer =====================
+        uint32_t s = 0, ph = 0, aph = 0;
+        const uint64_t adesc0 = smem_desc(sA, 16, 1024, 2);
+        const uint64_t bdesc0 = smem_desc(sST, 16, 512, 4);
+        const uint64_t axdesc = smem_desc(sAX, 128, 256, 0);
+        const uint64_t bxdesc0 = smem_desc(sST, 128, 256, 0);
+        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
+            for (int p = 0; p < 2; ++p) {
+#pragma unroll 1
+                for (int li = 0; li < 8; ++li) {
+                    const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
+                    mbar_wait(bar_aready, aph);
+                    aph ^= 1u;
+                    if (ld.xkind) {
+                        mbar_wait(bar_full(s), ph);
+                        tc_fence_after();
+                        if (elect_one()) {
+                            const uint64_t bx = bxdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
+                            for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                                const int nn = min(256, (int)ld.n - n0);
+                                umma_f16(tmem + n0, axdesc, bx + (uint64_t)((n0 * 32) >> 4), idesc_f16(TILE_M, nn), 0u);
+                            }
+                            umma_commit(bar_empty(s));
+                        }
+                        __syncwarp();
+                        if (++s == NST) { s = 0; ph ^= 1u; }
+                    }
+                    for (int n0 = 0; n0 < ld.n; n0 += 256) {
+                        const uint32_t id = idesc_f16(TILE_M, min(256, (int)ld.n - n0));
+                        const uint32_t dcol = tmem + n0;
+#pragma unroll 1
+                        for (int k2 = 0; k2 < 2 * ld.k32; ++k2) {
+                            const int kc = k2 >> 1;
+                            mbar_wait(bar_full(s), ph);
+                            tc_fence_after();
+                            if (elect_one()) {
+                                const uint64_t ad = adesc0 + (uint64_t)((kc >> 1) * (A_BLK >> 4) + (kc & 1) * 4);
+                                const uint64_t bd = bdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
+                                umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && k2 == 0) ? 0u : 1u);
+                                umma_f16(dcol, ad + 2, bd + 2, id, 1u);
+                                umma_commit(bar_empty(s));
+                            }
+                            __syncwarp();
+                            if (++s == NST) { s = 0; ph ^= 1u; }
+                        }
+                    }
+                    if (elect_one()) umma_commit(bar_dfull);
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===================== epilogue warps =====================
+        const int q = warp & 3, hc = warp >> 2;
+        const bool hi_thr = q < 2;                          // this warp's TMEM lanes hold the hi rows (else the lo rows)
+        const int rr = (q & 1) * 32 + lane;                 // real row of the tile
+        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
+        const int rx = rr & 7;
+        const uint32_t arow_hi = sA + (uint32_t)(rr >> 3) * 1024u + (uint32_t)rx * 128u;
+        const uint32_t arow_lo = arow_hi + 8u * 1024u;      // tile row rr + 64
+        float* xb_out = reinterpret_cast<float*>(sm + C::O_XB + warp * C::XB_WARP);
+        const float* xb_in = reinterpret_cast<const float*>(sm + C::O_XB + (warp ^ 2) * C::XB_WARP);
+        const int pair_bar = 2 + (q & 1) + 2 * hc;          // named barrier of the warp pair (q, q ^ 2)
+        const int keep0 = hc * 256 + (hi_thr ? 0 : 128);    // the 128 columns this thread finalises, in both sweeps
+        const int send0 = hc * 256 + (hi_thr ? 128 : 0);    // the 128 columns its partner finalises
+        const int etid = tid;
+        const int L = a.dec.L;
+        uint32_t dph = 0;
+        uint32_t mw[8][4];                                  // ReLU sign bits of this thread's 128 columns, per layer
+        // layer-4 input gradients of real row rr (written by the thread that finalises those columns, read back by the
+        // hi thread of column half 0 in the last step): per CTA [PARK_LD][TILE_M], column-major
+        float* park = a.dec.tc_park + (size_t)blockIdx.x * TILE_M * PARK_LD + rr;
+
+        auto signal_ready = [&]() {
+            tc_fence_before();
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_aready);
+        };
+        auto store32 = [&](uint32_t a_row, int col, const uint32_t* p) {
+            const uint32_t blk = a_row + (uint32_t)(col >> 6) * A_BLK;
+            const int cc0 = (col & 63) >> 3;
+#pragma unroll
+            for (int qq = 0; qq < 4; ++qq)
+                st_shared_v4(blk + (uint32_t)(((cc0 + qq) ^ rx) << 4), p[4 * qq], p[4 * qq + 1], p[4 * qq + 2], p[4 * qq + 3]);
+        };
+        // 32 FP32 values of columns [col, col + 32) of real row rr -> hi / lo FP16 halves in tile rows rr and rr + 64
+        auto store_split = [&](int col, const float (&f)[32]) {
+            uint32_t ph16[16], pl16[16];
+#pragma unroll
+            for (int c = 0; c < 16; ++c) {
+                const uint32_t h2 = pack_f16x2(f[2 * c], f[2 * c + 1]);
+                const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&h2));
+                ph16[c] = h2;
+                pl16[c] = pack_f16x2(f[2 * c] - hf.x, f[2 * c + 1] - hf.y);
+            }
+            store32(arow_hi, col, ph16);
+            store32(arow_lo, col, pl16);
+        };
+        // sum of the hi-row and lo-row accumulators of slice i of this thread's columns (warp-uniform validity flags)
+        auto combine = [&](int i, int ncols, float (&f)[32]) -> bool {
+            const int cs = send0 + 32 * i, ck = keep0 + 32 * i;
+            const bool s_ok = cs < ncols, k_ok = ck < ncols;
+            if (s_ok) {                                      // (one 32-register slice live at a time)
+                uint32_t vs[32];
+                tmem_ld32(trow + cs, vs);
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) xb_out[c * 32 + lane] = __uint_as_float(vs[c]);
+            }
+            uint32_t vk[32];
+            if (k_ok) tmem_ld32(trow + ck, vk);              // in flight across the barrier
+            named_bar_sync(pair_bar, 64);
+            if (k_ok) {
+                tmem_ld_wait();
+#pragma unroll
+                for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(vk[c]) + xb_in[c * 32 + lane];
+            }
+            named_bar_sync(pair_bar, 64);                    // slice buffers reusable
+            return k_ok;
+        };
+
+        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
+            // ---------------- tile rows ----------------
+            int obj = 0, row0 = 0, rows_valid = 0, M_obj = 0;
+            size_t jb = 0;
+            if (GN) {
+                obj = a.w.tile_obj[tb]; row0 = a.w.tile_row0[tb];
+                M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
+                const int K = a.w.prm.pose_only ? 0 : a.w.st[obj].K;
+                rows_valid = min(ROWS, M_obj + K - row0);
+                jb = (size_t)a.w.pts_off[obj] + (size_t)a.w.ray_off[obj] * a.w.prm.D;
+            } else {
+                const int64_t left = a.n - (int64_t)tb * ROWS;
+                rows_valid = (int)(left < ROWS ? left : ROWS);
+            }
+            const bool valid = rr < rows_valid;
+            float coef = 0.f, resid = 0.f;
+            if (hc == 0) {
+                const int trw = hi_thr ? rr : rr + 64;
+                const uint32_t ax = sAX + (uint32_t)(trw >> 3) * 256u + (uint32_t)rx * 16u;
+                if (hi_thr) {
+                    float x = 0.f, y = 0.f, z = 0.f;
+                    if (valid) {
+                        if (GN) {
+                            const float4 v = a.w.jrows[jb + row0 + rr];
+                            x = v.x; y = v.y; z = v.z; coef = v.w;
+                            if (row0 + rr >= M_obj) resid = a.w.jres[jb + row0 + rr];
+                        } else {
+                            const int64_t gr = (int64_t)tb * ROWS + rr;
+                            x = a.xyz[gr * 3 + 0]; y = a.xyz[gr * 3 + 1]; z = a.xyz[gr * 3 + 2];
+                        }
+                    }
+                    xyzs[rr] = make_float4(x, y, z, coef);
+                    __half xh, xl, yh, yl, zh, zl;
+                    split_f16(x, xh, xl); split_f16(y, yh, yl); split_f16(z, zh, zl);
+                    const __half one = __float2half_rn(1.f), zero = __float2half_rn(0.f);
+                    const __half2 c0a = __halves2half2(one, one), c0b = __halves2half2(xh, yh), c0c = __halves2half2(zh, xl),
+                                  c0d = __halves2half2(yl, zl);
+                    const __half2 c1a = __halves2half2(xh, yh), c1b = __halves2half2(zh, zero), c1z = __halves2half2(zero, zero);
+                    st_shared_v4(ax, *reinterpret_cast<const uint32_t*>(&c0a), *reinterpret_cast<const uint32_t*>(&c0b),
+                                 *reinterpret_cast<const uint32_t*>(&c0c), *reinterpret_cast<const uint32_t*>(&c0d));
+                    st_shared_v4(ax + 128u, *reinterpret_cast<const uint32_t*>(&c1a), *reinterpret_cast<const uint32_t*>(&c1b),
+                                 *reinterpret_cast<const uint32_t*>(&c1z), *reinterpret_cast<const uint32_t*>(&c1z));
+                } else {
+                    st_shared_v4(ax, 0u, 0u, 0u, 0u);
+                    st_shared_v4(ax + 128u, 0u, 0u, 0u, 0u);
+                }
+            }
+            signal_ready();
+
+            // ---------------- forward sweep ----------------
+            float sdf_y = 0.f;
+            for (int l = 0; l < 8; ++l) {
+                const bool last = (l == 7);
+                const int ncols = (l == 3) ? a.dec.h3p : HID;
+                mbar_wait(bar_dfull, dph);
+                dph ^= 1u;
+                tc_fence_after();
+                float part = 0.f;
+#pragma unroll 1
+                for (int i = 0; i < 4; ++i) {
+                    float f[32];
+                    uint32_t m = 0u;
+                    if (combine(i, ncols, f)) {
+                        const int ck = keep0 + 32 * i;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) {
+                            m = (m << 1) | (f[c] > 0.f ? 1u : 0u);   // bit (31 - c) set <=> pre-activation c positive
+                            f[c] = fmaxf(f[c], 0.f);
+                        }
+                        if (!last) {
+                            store_split(ck, f);
+                        } else {                              // layer 8 (1 x 512) folded into the last epilogue
+                            const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                const float4 wv = w4[c];
+                                part = fmaf(f[4 * c + 0], wv.x, part);
+                                part = fmaf(f[4 * c + 1], wv.y, part);
+                                part = fmaf(f[4 * c + 2], wv.z, part);
+                                part = fmaf(f[4 * c + 3], wv.w, part);
+                            }
+                        }
+                    }
+                    mw[l][i] = m;
+                }
+                if (!last) {
+                    signal_ready();
+                } else {
+                    parts[(hc * 2 + (hi_thr ? 0 : 1)) * ROWS + rr] = part;
+                    tc_fence_before();
+                    named_bar_sync(1, EPI_THREADS);
+                    sdf_y = tanhf(parts[rr] + parts[ROWS + rr] + parts[2 * ROWS + rr] + parts[3 * ROWS + rr] + a.dec.b8);
+                }
+            }
+
+            // ---------------- backward (input-gradient) sweep ----------------
+            {
+                // g7 = dy * w8 . relu'(a7) for this thread's 128 columns (no accumulator involved)
+                const float dyS = GSCALE * (1.f - sdf_y * sdf_y);
+#pragma unroll 1
+                for (int i = 0; i < 4; ++i) {
+                    const int ck = keep0 + 32 * i;
+                    const uint32_t m = mw[7][i];
+                    const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
+                    float f[32];
+#pragma unroll
+                    for (int c = 0; c < 8; ++c) {
+                        const float4 wv = w4[c];
+                        f[4 * c + 0] = ((m << (4 * c + 0)) & 0x80000000u) ? dyS * wv.x : 0.f;
+                        f[4 * c + 1] = ((m << (4 * c + 1)) & 0x80000000u) ? dyS * wv.y : 0.f;
+                        f[4 * c + 2] = ((m << (4 * c + 2)) & 0x80000000u) ? dyS * wv.z : 0.f;
+                        f[4 * c + 3] = ((m << (4 * c + 3)) & 0x80000000u) ? dyS * wv.w : 0.f;
+                    }
+                    store_split(ck, f);
+                }
+                signal_ready();
+
+                // steps l = 7..1: D = g_l W_l (hi + lo rows) -> sum -> mask with relu'(a_{l-1}) -> next A (hi / lo rows)
+                const int h3 = a.dec.h3, h3p = a.dec.h3p;
+                for (int l = 7; l >= 1; --l) {
+                    mbar_wait(bar_dfull, dph);
+                    dph ^= 1u;
+                    tc_fence_after();
+                    const bool split = (l == 4);             // columns >= h3 are d/d(input) (latent re-injection)
+#pragma unroll 1
+                    for (int i = 0; i < 4; ++i) {
+                        float f[32];
+                        if (!combine(i, HID, f)) continue;
+                        const int ck = keep0 + 32 * i;
+                        const uint32_t m = mw[l - 1][i];
+                        if (split && ck >= h3p) {            // pure input-gradient columns: parked, not propagated
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) park[(ck + c - h3) * TILE_M] = f[c];
+                            continue;
+                        }
+                        if (split && ck + 32 > h3) {         // the slice that straddles h3
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) {
+                                const bool hid = (ck + c) < h3;
+                                if (!hid) park[(ck + c - h3) * TILE_M] = f[c];
+                                if (!hid || !((m << c) & 0x80000000u)) f[c] = 0.f;
+                            }
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < 32; ++c)
+                                if (!((m << c) & 0x80000000u)) f[c] = 0.f;
+                        }
+                        store_split(ck, f);
+                    }
+                    signal_ready();
+                }
+
+                // last step: D[:, 0 .. in_dim) = g_0 W_0; jac = (D + parked layer-4 part) / GSCALE.  The columns lie in
+                // column half 0: its lo warps send, its hi warps finalise; column half 1 has nothing to do.
+                mbar_wait(bar_dfull, dph);
+                dph ^= 1u;
+                tc_fence_after();
+                const float inv_s = 1.f / GSCALE;
+                const int in_dim = L + 3;
+                if (hc == 0) {
+                    float* jr = jrow + rr * JLD;
+                    const float cf = GN ? xyzs[rr].w : 1.f;
+                    const int o = GN ? POSE : 0;             // stand-alone rows are [code | xyz], GN rows [pose 7 | code]
+                    float gxyz[3] = {0.f, 0.f, 0.f};
+#pragma unroll 1
+                    for (int i = 0; i < 3; ++i) {
+                        float f[32];
+                        const bool k_ok = combine(i, 96, f);  // (hi threads keep columns 32 i .., lo threads only send)
+                        if (!hi_thr || !k_ok) continue;
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) {
+                            const int col = 32 * i + c;
+                            if (col < in_dim) {
+                                const float g = (f[c] + park[col * TILE_M]) * inv_s;
+                                if (col < L) jr[o + col] = cf * g;
+                                else if (GN) gxyz[col - L] = g;
+                                else jr[col] = g;
+                            }
+                        }
+                    }
+                    if (GN && hi_thr) {
+                        const float4 pc = xyzs[rr];
+                        build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
+                        for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;
+                    }
+                }
+                tc_fence_before();
+            }
+
+            if (!GN) {
+                named_bar_sync(1, EPI_THREADS);
+                const int in_dim = L + 3;
+                const int64_t g0 = (int64_t)tb * ROWS;
+                if (hc == 0 && hi_thr && valid) a.out[g0 + rr] = sdf_y;
+                for (int e = etid; e < rows_valid * in_dim; e += EPI_THREADS) {
+                    const int row = e / in_dim, i = e - row * in_dim;
+                    a.jac_out[(g0 + row) * in_dim + i] = jrow[row * JLD + i];
+                }
+                named_bar_sync(1, EPI_THREADS);
+            } else {
+                // ---- residual weights, then J^T J / J^T r of the tile's 64 rows (optimizer.py:163-169) ----
+                const GnWork& w = a.w;
+                const ObjState& so = w.st[obj];
+                const int K = w.prm.pose_only ? 0 : so.K;
+                const float w_s = (w.prm.pose_only ? 1.f : w.prm.k2) / (float)so.M_active;
+                const float w_r = w.prm.k1 / (float)K;
+                float ls = 0.f, lr = 0.f;
+                if (hc == 0 && hi_thr) {
+                    float wr = 0.f, rt = 0.f;
+                    if (valid) {
+                        const int r_obj = row0 + rr;
+                        if (r_obj < M_obj) {                                  // surface row: residual = SDF itself
+                            w.sres[w.pts_off[obj] + r_obj] = sdf_y;
+                            rt = w.prm.pose_only ? sdf_y : huber_res(sdf_y, w.prm.b2);
+                            if (coef != 0.f) { wr = w_s; ls = rt * rt; }
+                        } else {                                              // render row
+                            rt = huber_res(resid, w.prm.b1);
+                            wr = w_r;
+                            lr = rt * rt;
+                        }
+                    }
+                    wrows[rr] = wr;
+                    rts[rr] = rt;
+                    for (int o = 16; o > 0; o >>= 1) {
+                        ls += __shfl_xor_sync(0xffffffffu, ls, o);
+                        lr += __shfl_xor_sync(0xffffffffu, lr, o);
+                    }
+                    if (lane == 0) { parts[q] = ls; parts[2 + q] = lr; }      // q in {0, 1}
+                }
+                named_bar_sync(1, EPI_THREADS);
+                const int n = POSE + L;
+                const int nb = (n + 3) >> 2;
+                const int nblk = nb * (nb + 1) / 2;
+                float* part = w.partials + ((size_t)obj * w.jgroups_max + (row0 / ROWS)) * PART_STRIDE;
+                if (etid < nblk) {
+                    int bi = 0, rem = etid;
+                    while (rem >= nb - bi) { rem -= nb - bi; ++bi; }
+                    const int bj = bi + rem;
+                    float acc[4][4];
+#pragma unroll
+                    for (int p = 0; p < 4; ++p)
+#pragma unroll
+                        for (int qq = 0; qq < 4; ++qq) acc[p][qq] = 0.f;
+                    const float* ja = jrow + 4 * bi;
+                    const float* jb4 = jrow + 4 * bj;
+#pragma unroll 4
+                    for (int row = 0; row < ROWS; ++row) {
+                        const float wr = wrows[row];
+                        const float4 av = *reinterpret_cast<const float4*>(ja + row * JLD);
+                        const float4 bv = *reinterpret_cast<const float4*>(jb4 + row * JLD);
+                        const float a4[4] = {wr * av.x, wr * av.y, wr * av.z, wr * av.w};
+                        const float b4[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                        for (int p = 0; p < 4; ++p)
+#pragma unroll
+                            for (int qq = 0; qq < 4; ++qq) acc[p][qq] = fmaf(a4[p], b4[qq], acc[p][qq]);
+                    }
+#pragma unroll
+                    for (int p = 0; p < 4; ++p)
+#pragma unroll
+                        for (int qq = 0; qq < 4; ++qq) {
+                            const int i = 4 * bi + p, j = 4 * bj + qq;
+                            if (i < n && j < n) {
+                                part[i * n + j] = acc[p][qq];
+                                if (bi != bj) part[j * n + i] = acc[p][qq];
+                            }
+                        }
+                } else {
+                    for (int i = etid - nblk; i < n; i += EPI_THREADS - nblk) {
+                        float sacc = 0.f;
+                        for (int row = 0; row < ROWS; ++row)
+                            sacc = fmaf(-wrows[row] * jrow[row * JLD + i], rts[row], sacc);
+                        part[n * n + i] = sacc;
+                    }
+                }
+                if (etid == 0) {
+                    part[PART_LOSS] = parts[0] + parts[1];
+                    part[PART_LOSS + 1] = parts[2] + parts[3];
+                }
+                named_bar_sync(1, EPI_THREADS);
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) {
+        __syncwarp();
+        tc_fence_after();
+        tmem_dealloc(tmem, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // extra blocks of layers 0 and 4 for the single-code entry points (gn_device.cuh: pack_extra_row; the GN
 // drivers build theirs inside k_gn_prep / k_gn_solve)
 // ------------------------------------------------------------------------------------------------
@@ -1191,6 +1717,8 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
     TC_ATTR(0) TC_ATTR(1) TC_ATTR(2) TC_ATTR(3) TC_ATTR(4) TC_ATTR(5)
 #undef TC_ATTR
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_refine, cudaFuncAttributeMaxDynamicSharedMemorySize, RCfg::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
     if (e != cudaSuccess) {
         g_tc_err = cudaGetErrorString(e);
         cudaFree(dev);
@@ -1259,6 +1787,26 @@ int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st) {
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
     launch_tc<3>(a, sm_count, st);
+    return 1;
+}
+
+int tc_launch_sdf_jac_exact(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
+                            const float* c4, float* sdf_out, float* jac_out, cudaStream_t st) {
+    using namespace tc;
+    k_tc_pack_extra<<<dim3(1, 2), HID, 0, st>>>(dec, c0, c4, dec.tc_xtra1);
+    TcArgs a{};
+    a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
+    a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
+    a.n_tiles = (int)((n + XCfg::ROWS - 1) / XCfg::ROWS);
+    k_tc_jacx<false><<<std::min(std::min(a.n_tiles, sm_count), PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
+    return 2;
+}
+
+int tc_launch_gn_jac_exact(const GnWork& w, int sm_count, cudaStream_t st) {
+    using namespace tc;
+    TcArgs a{};
+    a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
+    k_tc_jacx<true><<<std::min(sm_count, PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
     return 1;
 }
 

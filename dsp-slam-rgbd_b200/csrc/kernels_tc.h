@@ -20,6 +20,10 @@ int tc_launch_sdf_jac(const DecoderDev& dec, int sm_count, const float* xyz, int
                       const float* c4, float* sdf_out, float* jac_out, int wsplit, cudaStream_t st);
 int tc_launch_gn_fwd(const GnWork& w, int sm_count, cudaStream_t st);
 int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st);
+// FP32-grade SDF + Jacobian on the tensor cores (hi/lo operand pairs, 64-row tiles): DSPSLAM_MODE_TC_EXACT
+int tc_launch_sdf_jac_exact(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
+                            const float* c4, float* sdf_out, float* jac_out, cudaStream_t st);
+int tc_launch_gn_jac_exact(const GnWork& w, int sm_count, cudaStream_t st);
 int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st);
 
 }  // namespace dsp

@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libdspslam_sm100.so")
 
-MODE_FP32, MODE_TC, MODE_TC_FAST = 0, 1, 4
+MODE_FP32, MODE_TC, MODE_TC_FAST, MODE_TC_EXACT = 0, 1, 4, 5
 ST_OK, ST_FEW_POINTS, ST_NAN = 0, 1, 2
 GRID_REFERENCE_SHEAR, GRID_LATTICE = 0, 1
 DBG_STRIDE = 5120

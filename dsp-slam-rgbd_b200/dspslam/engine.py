@@ -15,6 +15,7 @@ from .packer import check_supported, check_variant, effective_weights
 
 _MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE_TC: N.MODE_TC,
           "tc_fast": N.MODE_TC_FAST, N.MODE_TC_FAST: N.MODE_TC_FAST,
+          "tc_exact": N.MODE_TC_EXACT, N.MODE_TC_EXACT: N.MODE_TC_EXACT,
           "mix_fwd_tc": 2, "mix_jac_tc": 3}     # diagnostic mixes (tools/free_run_stats.py)
 
 

@@ -62,8 +62,11 @@ enum {
                             * measures that keep a GN step on the FP32 reference's: ray samples next to a decision
                             * threshold are evaluated a second time at FP32 grade (joint_params.refine_window), and the
                             * SDF+Jacobian kernel multiplies by hi(W) + lo(W) (two MMA passes per K chunk)             */
-    DSPSLAM_MODE_TC_FAST = 4 /* tcgen05, single FP16 pass everywhere (round-1 arithmetic): ~15 % faster, per-step
-                              * parity with the reference 88 % instead of >= 95 % of the steps           */
+    DSPSLAM_MODE_TC_FAST = 4, /* tcgen05, single FP16 pass everywhere (round-1 arithmetic): ~12 % faster, per-step
+                               * parity with the reference 88 % instead of >= 95 % of the steps          */
+    DSPSLAM_MODE_TC_EXACT = 5 /* tcgen05 at FP32 grade where it matters: the SDF+Jacobian rows are evaluated with both
+                               * operands as hi+lo FP16 pairs in both sweeps (k_tc_jacx, 64-row tiles; ~4x the tensor
+                               * work per row), the ray samples as in DSPSLAM_MODE_TC                                  */
 };
 
 /* per-object status written by the Gauss-Newton drivers */

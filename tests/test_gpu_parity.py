@@ -109,6 +109,30 @@ def test_queries_ragged_sizes_vs_oracle(mode, n, eng, odec):
         _jac_check(mode, j.cpu().numpy(), jo)
 
 
+@pytest.mark.parametrize("n", [1, 63, 64, 65, 777, 9473, 38011])
+def test_exact_mode_queries_ragged_sizes_vs_oracle(n, eng, odec):
+    """DSPSLAM_MODE_TC_EXACT (64-row tiles of hi/lo stacked rows): tile counts 1, 2, 13, 149 (one more than the grid)
+    and 594; SDF and every Jacobian entry at FP32 grade except rows with a ReLU unit at its kink (<= 1 in 1 000)."""
+    rng = np.random.default_rng(n + 1)
+    code = (0.3 * rng.normal(size=64)).astype(np.float32)
+    x = rng.uniform(-0.8, 0.8, size=(n, 3)).astype(np.float32)
+    so, jo = odec.sdf_jacobian(code, x)
+    s, j = eng.sdf_jac(code, x, mode="tc_exact")
+    assert np.abs(s.cpu().numpy() - so).max() < 2e-5
+    err = np.abs(j.cpu().numpy() - jo)
+    assert (err.max(axis=1) > 1e-4).sum() <= max(1, n // 1000), (err.max(axis=1) > 1e-4).sum()
+    assert np.sqrt((err ** 2).mean()) < 5e-5 and err.max() < 0.2
+
+
+def test_exact_mode_c2_sized_steps_vs_reference(eng):
+    """One C2-sized detection through the exact mode, teacher-forced against the reference (H, b, next state)."""
+    from dspslam import synth
+    g = load("c2_obj1.npz")
+    det = synth.make_kitti_detection(1, M=2048, n_bg=200)
+    g.update(in_pts=det["pts"], in_rays=det["rays"], in_depth=det["depth"])
+    _teacher_forced(eng, "tc_exact", g, synth.kitti_config(), range(10), 1e-2, 3e-2)
+
+
 @pytest.mark.parametrize("mode", MODES)
 def test_empty_query(mode, eng):
     code = np.zeros(64, np.float32)
@@ -381,6 +405,18 @@ def test_grid_g64_vs_reference_golden(mode, eng):
     g = load("grid_sdf_g64.npz")
     out = eng.grid_sdf(g["code"], 64, mode=mode).cpu().numpy().reshape(64, 64, 64)
     assert np.abs(out - g["sdf"]).max() < TOL_SDF[mode]
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_grid_g256_slab_vs_reference_golden(mode, eng):
+    """BASELINE C4 size against the reference itself: four x-planes (262 144 voxels) of the G = 256 grid, the
+    reference's own sheared `create_voxel_grid(256)` through its own `decode_sdf` (oracle/make_golden_grid256.py)."""
+    g = load("grid_sdf_g256_slab.npz")
+    G_, i0, i1 = int(g["G"]), int(g["i0"]), int(g["i1"])
+    out = eng.grid_sdf(g["code"], G_, i0=i0, i1=i1, mode=mode).cpu().numpy()
+    assert out.shape == g["sdf"].shape
+    assert np.abs(out - g["sdf"]).max() < TOL_SDF[mode]
+    assert g["sdf"].min() < 0 < g["sdf"].max()
 
 
 def test_grid_sharded_equals_single(eng):
