@@ -1044,7 +1044,7 @@ struct XCfg {
 static_assert(XCfg::ROWS * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the activation tile");
 
 template <bool GN>
-__global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArgs a) {
+__global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
     using C = XCfg;
     constexpr int NST = C::NST;
     constexpr int ROWS = C::ROWS;
