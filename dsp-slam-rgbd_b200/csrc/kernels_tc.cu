@@ -1043,8 +1043,15 @@ struct XCfg {
 };
 static_assert(XCfg::ROWS * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the activation tile");
 
+// timing experiments (wrong numerics on purpose; tools/bench_exact.py): -DDSP_X_EXP=1 no lane-half exchange,
+// 2 no activation stores, 3 no lo(W) pass
+#ifndef DSP_X_EXP
+#define DSP_X_EXP 0
+#endif
+constexpr int XREP = (DSP_X_EXP == 3) ? 1 : 2;
+
 template <bool GN>
-__global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
+__global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArgs a) {
     using C = XCfg;
     constexpr int NST = C::NST;
     constexpr int ROWS = C::ROWS;
@@ -1108,14 +1115,14 @@ __global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
                     for (int n0 = 0; n0 < ld.n; n0 += 256) {
                         const uint32_t bytes = (uint32_t)min(256, (int)ld.n - n0) * 64u;
 #pragma unroll 1
-                        for (int k2 = 0; k2 < 2 * ld.k32; ++k2) {
+                        for (int k2 = 0; k2 < XREP * ld.k32; ++k2) {
                             mbar_wait(bar_empty(s), ph ^ 1u);
                             if (elect_one()) {
                                 mbar_expect_tx(bar_full(s), bytes);
-                                bulk_g2s(sST + s * STAGE_BYTES, (k2 & 1) ? src_lo : src_hi, bytes, bar_full(s));
+                                bulk_g2s(sST + s * STAGE_BYTES, (XREP == 2 && (k2 & 1)) ? src_lo : src_hi, bytes, bar_full(s));
                             }
                             __syncwarp();
-                            if (k2 & 1) { src_hi += bytes; src_lo += bytes; }
+                            if (XREP == 1 || (k2 & 1)) { src_hi += bytes; src_lo += bytes; }
                             if (++s == NST) { s = 0; ph ^= 1u; }
                         }
                     }
@@ -1154,8 +1161,8 @@ __global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
                         const uint32_t id = idesc_f16(TILE_M, min(256, (int)ld.n - n0));
                         const uint32_t dcol = tmem + n0;
 #pragma unroll 1
-                        for (int k2 = 0; k2 < 2 * ld.k32; ++k2) {
-                            const int kc = k2 >> 1;
+                        for (int k2 = 0; k2 < XREP * ld.k32; ++k2) {
+                            const int kc = (XREP == 2) ? (k2 >> 1) : k2;
                             mbar_wait(bar_full(s), ph);
                             tc_fence_after();
                             if (elect_one()) {
@@ -1211,22 +1218,29 @@ __global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
         };
         // 32 FP32 values of columns [col, col + 32) of real row rr -> hi / lo FP16 halves in tile rows rr and rr + 64
         auto store_split = [&](int col, const float (&f)[32]) {
-            uint32_t ph16[16], pl16[16];
+            if (DSP_X_EXP == 2) return;
+            const uint32_t blk_hi = arow_hi + (uint32_t)(col >> 6) * A_BLK, blk_lo = arow_lo + (uint32_t)(col >> 6) * A_BLK;
+            const int cc0 = (col & 63) >> 3;
 #pragma unroll
-            for (int c = 0; c < 16; ++c) {
-                const uint32_t h2 = pack_f16x2(f[2 * c], f[2 * c + 1]);
-                const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&h2));
-                ph16[c] = h2;
-                pl16[c] = pack_f16x2(f[2 * c] - hf.x, f[2 * c + 1] - hf.y);
+            for (int qq = 0; qq < 4; ++qq) {                 // 8 columns = one 16-byte chunk per half at a time
+                uint32_t h[4], l[4];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const float f0 = f[8 * qq + 2 * c], f1 = f[8 * qq + 2 * c + 1];
+                    h[c] = pack_f16x2(f0, f1);
+                    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&h[c]));
+                    l[c] = pack_f16x2(f0 - hf.x, f1 - hf.y);
+                }
+                const uint32_t off = (uint32_t)(((cc0 + qq) ^ rx) << 4);
+                st_shared_v4(blk_hi + off, h[0], h[1], h[2], h[3]);
+                st_shared_v4(blk_lo + off, l[0], l[1], l[2], l[3]);
             }
-            store32(arow_hi, col, ph16);
-            store32(arow_lo, col, pl16);
         };
         // sum of the hi-row and lo-row accumulators of slice i of this thread's columns (warp-uniform validity flags)
         auto combine = [&](int i, int ncols, float (&f)[32]) -> bool {
             const int cs = send0 + 32 * i, ck = keep0 + 32 * i;
             const bool s_ok = cs < ncols, k_ok = ck < ncols;
-            if (s_ok) {                                      // (one 32-register slice live at a time)
+            if (s_ok && DSP_X_EXP != 1) {                    // (one 32-register slice live at a time)
                 uint32_t vs[32];
                 tmem_ld32(trow + cs, vs);
                 tmem_ld_wait();
@@ -1235,13 +1249,13 @@ __global__ void __maxnreg__(200) k_tc_jacx(const __grid_constant__ TcArgs a) {
             }
             uint32_t vk[32];
             if (k_ok) tmem_ld32(trow + ck, vk);              // in flight across the barrier
-            named_bar_sync(pair_bar, 64);
+            if (DSP_X_EXP != 1) named_bar_sync(pair_bar, 64);
             if (k_ok) {
                 tmem_ld_wait();
 #pragma unroll
-                for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(vk[c]) + xb_in[c * 32 + lane];
+                for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(vk[c]) + (DSP_X_EXP != 1 ? xb_in[c * 32 + lane] : 0.f);
             }
-            named_bar_sync(pair_bar, 64);                    // slice buffers reusable
+            if (DSP_X_EXP != 1) named_bar_sync(pair_bar, 64);   // slice buffers reusable
             return k_ok;
         };
 
