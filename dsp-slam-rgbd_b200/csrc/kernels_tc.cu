@@ -1027,13 +1027,13 @@ __global__ void __launch_bounds__(NT, 1) k_tc_refine(const __grid_constant__ TcA
 // Cost: 4 single-pass rows of tensor work per real row and a heavier epilogue - about 4x the FP16 kernel per row.
 // ------------------------------------------------------------------------------------------------
 struct XCfg {
-    static constexpr int NST = 3;
+    static constexpr int NST = 4;
     static constexpr int ROWS = REFINE_ROWS;                        // real rows per tile
     static constexpr int O_AX = A_BYTES;
     static constexpr int O_ST = O_AX + AX_BYTES;
-    static constexpr int XB_WARP = 32 * 32 * 4;
+    static constexpr int XB_BYTES = 2 * (2 * 2048) + 2 * (2 * 4096);   // slice buffers of the four warp pairs
     static constexpr int O_XB = O_ST + NST * STAGE_BYTES;
-    static constexpr int O_W8 = O_XB + 8 * XB_WARP;
+    static constexpr int O_W8 = O_XB + XB_BYTES;
     static constexpr int O_XYZ = O_W8 + 2048;                       // float4 x 64
     static constexpr int O_PART = O_XYZ + 1024;                     // 4 x 64 floats
     static constexpr int O_WROW = O_PART + 1024;                    // 64 floats
@@ -1077,6 +1077,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
         for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
         mbar_init(bar_aready, 8);
         mbar_init(bar_dfull, 1);
+        for (int i = 0; i < 16; ++i) mbar_init(bar0 + 128u + 8u * i, 1);     // slice buffers: full / empty per pair
         fence_mbar_init();
     }
     if (warp == 9) {
@@ -1183,24 +1184,33 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
         }
     } else {
         // ===================== epilogue warps =====================
+        // Warps q and q + 2 (same column half hc) hold the hi rows and the lo rows of the same 32 real rows.  One of the
+        // two FINALISES the pair's 256 columns - adds the partner's accumulators to its own, applies the ReLU (mask),
+        // splits into hi / lo and writes the next A operand - the other only SENDS its accumulators through a
+        // double-buffered shared-memory slice.  The finaliser is the hi warp in column half 0 and the lo warp in
+        // column half 1, so every warp scheduler has one heavy warp.  A lo-row accumulator is ~2^-11 of the hi-row one:
+        // the lo warps send theirs as FP16 pairs (half the traffic, 2^-22 relative), the hi warps send FP32.
         const int q = warp & 3, hc = warp >> 2;
         const bool hi_thr = q < 2;                          // this warp's TMEM lanes hold the hi rows (else the lo rows)
+        const bool fin = (hc == 0) ? hi_thr : !hi_thr;      // finaliser of the pair's columns [256 hc, 256 hc + 256)
         const int rr = (q & 1) * 32 + lane;                 // real row of the tile
         const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
         const int rx = rr & 7;
         const uint32_t arow_hi = sA + (uint32_t)(rr >> 3) * 1024u + (uint32_t)rx * 128u;
         const uint32_t arow_lo = arow_hi + 8u * 1024u;      // tile row rr + 64
-        float* xb_out = reinterpret_cast<float*>(sm + C::O_XB + warp * C::XB_WARP);
-        const float* xb_in = reinterpret_cast<const float*>(sm + C::O_XB + (warp ^ 2) * C::XB_WARP);
-        const int pair_bar = 2 + (q & 1) + 2 * hc;          // named barrier of the warp pair (q, q ^ 2)
-        const int keep0 = hc * 256 + (hi_thr ? 0 : 128);    // the 128 columns this thread finalises, in both sweeps
-        const int send0 = hc * 256 + (hi_thr ? 128 : 0);    // the 128 columns its partner finalises
+        const int col0 = hc * 256;
+        const int pair = (q & 1) + 2 * hc;
+        // slices: pairs 0, 1 (senders = lo warps, FP16 pairs): 2 x 2 KB each; pairs 2, 3 (senders = hi warps, FP32): 2 x 4 KB
+        uint8_t* xb = sm + C::O_XB + (hc == 0 ? pair * 4096 : 8192 + (pair - 2) * 8192);
+        const int xb_bytes = (hc == 0) ? 2048 : 4096;
+        const uint32_t xbar = bar0 + 128u + 32u * pair;     // full[0], full[1], empty[0], empty[1]
+        uint32_t xi = 0, xph = 0;                           // slice buffer in use and its phase (same sequence in both warps)
         const int etid = tid;
         const int L = a.dec.L;
         uint32_t dph = 0;
-        uint32_t mw[8][4];                                  // ReLU sign bits of this thread's 128 columns, per layer
-        // layer-4 input gradients of real row rr (written by the thread that finalises those columns, read back by the
-        // hi thread of column half 0 in the last step): per CTA [PARK_LD][TILE_M], column-major
+        uint32_t mw[8][8];                                  // finaliser: ReLU sign bits of the pair's 256 columns, per layer
+        // layer-4 input gradients of real row rr (written by the finaliser of column half 1, read back by the one of
+        // column half 0 in the last step): per CTA [PARK_LD][TILE_M], column-major
         float* park = a.dec.tc_park + (size_t)blockIdx.x * TILE_M * PARK_LD + rr;
 
         auto signal_ready = [&]() {
@@ -1208,13 +1218,6 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0) mbar_arrive(bar_aready);
-        };
-        auto store32 = [&](uint32_t a_row, int col, const uint32_t* p) {
-            const uint32_t blk = a_row + (uint32_t)(col >> 6) * A_BLK;
-            const int cc0 = (col & 63) >> 3;
-#pragma unroll
-            for (int qq = 0; qq < 4; ++qq)
-                st_shared_v4(blk + (uint32_t)(((cc0 + qq) ^ rx) << 4), p[4 * qq], p[4 * qq + 1], p[4 * qq + 2], p[4 * qq + 3]);
         };
         // 32 FP32 values of columns [col, col + 32) of real row rr -> hi / lo FP16 halves in tile rows rr and rr + 64
         auto store_split = [&](int col, const float (&f)[32]) {
@@ -1236,27 +1239,50 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 st_shared_v4(blk_lo + off, l[0], l[1], l[2], l[3]);
             }
         };
-        // sum of the hi-row and lo-row accumulators of slice i of this thread's columns (warp-uniform validity flags)
-        auto combine = [&](int i, int ncols, float (&f)[32]) -> bool {
-            const int cs = send0 + 32 * i, ck = keep0 + 32 * i;
-            const bool s_ok = cs < ncols, k_ok = ck < ncols;
-            if (s_ok && DSP_X_EXP != 1) {                    // (one 32-register slice live at a time)
-                uint32_t vs[32];
-                tmem_ld32(trow + cs, vs);
-                tmem_ld_wait();
+        auto x_advance = [&]() { if (++xi == 2) { xi = 0; xph ^= 1u; } };
+        // sender: this warp's accumulators of columns [col, col + 32) into the next slice buffer
+        auto send_slice = [&](int col) {
+            uint32_t v[32];
+            tmem_ld32(trow + col, v);
+            tmem_ld_wait();
+            mbar_wait(xbar + 16u + 8u * xi, xph ^ 1u);       // the finaliser has read what this buffer held
+            if (hc == 0) {
+                uint32_t* dst = reinterpret_cast<uint32_t*>(xb + xi * xb_bytes);
 #pragma unroll
-                for (int c = 0; c < 32; ++c) xb_out[c * 32 + lane] = __uint_as_float(vs[c]);
-            }
-            uint32_t vk[32];
-            if (k_ok) tmem_ld32(trow + ck, vk);              // in flight across the barrier
-            if (DSP_X_EXP != 1) named_bar_sync(pair_bar, 64);
-            if (k_ok) {
-                tmem_ld_wait();
+                for (int c = 0; c < 16; ++c)
+                    dst[c * 32 + lane] = pack_f16x2(__uint_as_float(v[2 * c]), __uint_as_float(v[2 * c + 1]));
+            } else {
+                uint32_t* dst = reinterpret_cast<uint32_t*>(xb + xi * xb_bytes);
 #pragma unroll
-                for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(vk[c]) + (DSP_X_EXP != 1 ? xb_in[c * 32 + lane] : 0.f);
+                for (int c = 0; c < 32; ++c) dst[c * 32 + lane] = v[c];
             }
-            if (DSP_X_EXP != 1) named_bar_sync(pair_bar, 64);   // slice buffers reusable
-            return k_ok;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(xbar + 8u * xi);
+            x_advance();
+        };
+        // finaliser: own accumulators of the slice + the partner's
+        auto recv_slice = [&](int col, float (&f)[32]) {
+            uint32_t v[32];
+            tmem_ld32(trow + col, v);
+            mbar_wait(xbar + 8u * xi, xph);
+            tmem_ld_wait();
+            if (hc == 0) {
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(xb + xi * xb_bytes);
+#pragma unroll
+                for (int c = 0; c < 16; ++c) {
+                    const uint32_t h2 = src[c * 32 + lane];
+                    const float2 p = __half22float2(*reinterpret_cast<const __half2*>(&h2));
+                    f[2 * c] = __uint_as_float(v[2 * c]) + p.x;
+                    f[2 * c + 1] = __uint_as_float(v[2 * c + 1]) + p.y;
+                }
+            } else {
+                const float* src = reinterpret_cast<const float*>(xb + xi * xb_bytes);
+#pragma unroll
+                for (int c = 0; c < 32; ++c) f[c] = __uint_as_float(v[c]) + src[c * 32 + lane];
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(xbar + 16u + 8u * xi);
+            x_advance();
         };
 
         for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
@@ -1317,40 +1343,41 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 dph ^= 1u;
                 tc_fence_after();
                 float part = 0.f;
+                const int nsl = min(8, max(0, (ncols - col0) >> 5));       // 32-column slices of this pair in the layer
 #pragma unroll 1
-                for (int i = 0; i < 4; ++i) {
+                for (int i = 0; i < nsl; ++i) {
+                    const int ck = col0 + 32 * i;
+                    if (!fin) { send_slice(ck); continue; }
                     float f[32];
+                    recv_slice(ck, f);
                     uint32_t m = 0u;
-                    if (combine(i, ncols, f)) {
-                        const int ck = keep0 + 32 * i;
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) {
-                            m = (m << 1) | (f[c] > 0.f ? 1u : 0u);   // bit (31 - c) set <=> pre-activation c positive
-                            f[c] = fmaxf(f[c], 0.f);
-                        }
-                        if (!last) {
-                            store_split(ck, f);
-                        } else {                              // layer 8 (1 x 512) folded into the last epilogue
-                            const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                const float4 wv = w4[c];
-                                part = fmaf(f[4 * c + 0], wv.x, part);
-                                part = fmaf(f[4 * c + 1], wv.y, part);
-                                part = fmaf(f[4 * c + 2], wv.z, part);
-                                part = fmaf(f[4 * c + 3], wv.w, part);
-                            }
-                        }
+                    for (int c = 0; c < 32; ++c) {
+                        m = (m << 1) | (f[c] > 0.f ? 1u : 0u);       // bit (31 - c) set <=> pre-activation c positive
+                        f[c] = fmaxf(f[c], 0.f);
                     }
                     mw[l][i] = m;
+                    if (!last) {
+                        store_split(ck, f);
+                    } else {                                  // layer 8 (1 x 512) folded into the last epilogue
+                        const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 wv = w4[c];
+                            part = fmaf(f[4 * c + 0], wv.x, part);
+                            part = fmaf(f[4 * c + 1], wv.y, part);
+                            part = fmaf(f[4 * c + 2], wv.z, part);
+                            part = fmaf(f[4 * c + 3], wv.w, part);
+                        }
+                    }
                 }
                 if (!last) {
                     signal_ready();
                 } else {
-                    parts[(hc * 2 + (hi_thr ? 0 : 1)) * ROWS + rr] = part;
+                    if (fin) parts[hc * ROWS + rr] = part;
                     tc_fence_before();
                     named_bar_sync(1, EPI_THREADS);
-                    sdf_y = tanhf(parts[rr] + parts[ROWS + rr] + parts[2 * ROWS + rr] + parts[3 * ROWS + rr] + a.dec.b8);
+                    sdf_y = tanhf(parts[rr] + parts[ROWS + rr] + a.dec.b8);
                 }
             }
 
@@ -1359,8 +1386,8 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 // g7 = dy * w8 . relu'(a7) for this thread's 128 columns (no accumulator involved)
                 const float dyS = GSCALE * (1.f - sdf_y * sdf_y);
 #pragma unroll 1
-                for (int i = 0; i < 4; ++i) {
-                    const int ck = keep0 + 32 * i;
+                for (int i = 0; i < 8 && fin; ++i) {
+                    const int ck = col0 + 32 * i;
                     const uint32_t m = mw[7][i];
                     const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
                     float f[32];
@@ -1384,10 +1411,11 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                     tc_fence_after();
                     const bool split = (l == 4);             // columns >= h3 are d/d(input) (latent re-injection)
 #pragma unroll 1
-                    for (int i = 0; i < 4; ++i) {
+                    for (int i = 0; i < 8; ++i) {
+                        const int ck = col0 + 32 * i;
+                        if (!fin) { send_slice(ck); continue; }
                         float f[32];
-                        if (!combine(i, HID, f)) continue;
-                        const int ck = keep0 + 32 * i;
+                        recv_slice(ck, f);
                         const uint32_t m = mw[l - 1][i];
                         if (split && ck >= h3p) {            // pure input-gradient columns: parked, not propagated
 #pragma unroll
@@ -1412,7 +1440,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 }
 
                 // last step: D[:, 0 .. in_dim) = g_0 W_0; jac = (D + parked layer-4 part) / GSCALE.  The columns lie in
-                // column half 0: its lo warps send, its hi warps finalise; column half 1 has nothing to do.
+                // column half 0 (lo warps send, hi warps finalise); column half 1 has nothing to do.
                 mbar_wait(bar_dfull, dph);
                 dph ^= 1u;
                 tc_fence_after();
@@ -1425,9 +1453,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                     float gxyz[3] = {0.f, 0.f, 0.f};
 #pragma unroll 1
                     for (int i = 0; i < 3; ++i) {
+                        if (!fin) { send_slice(32 * i); continue; }
                         float f[32];
-                        const bool k_ok = combine(i, 96, f);  // (hi threads keep columns 32 i .., lo threads only send)
-                        if (!hi_thr || !k_ok) continue;
+                        recv_slice(32 * i, f);
 #pragma unroll
                         for (int c = 0; c < 32; ++c) {
                             const int col = 32 * i + c;
@@ -1439,7 +1467,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                             }
                         }
                     }
-                    if (GN && hi_thr) {
+                    if (GN && fin) {
                         const float4 pc = xyzs[rr];
                         build_pose_row(jr, cf * gxyz[0], cf * gxyz[1], cf * gxyz[2], pc.x, pc.y, pc.z);
                         for (int c = POSE + L; c < JLD; ++c) jr[c] = 0.f;
