@@ -59,7 +59,7 @@ struct ObjState {
     int K;            // render rows this iteration
     int M_active;     // surface rows in use (pose-only inlier cut)
     float sdf_loss, render_loss, loss;
-    int rf_rows;      // ray samples of this iteration queued for the FP32-grade second evaluation (kernels_tc.cu: k_tc_refine)
+    int rf_rows;      // ray samples of this iteration queued for the FP32-grade second evaluation (kernels_tc.cu: k_tc_jacx<2>)
     int ph_rows[MAX_PHASES];   // in-ball samples handed to the decoder in each ray phase of this iteration
 };
 

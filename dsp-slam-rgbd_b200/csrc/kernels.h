@@ -32,7 +32,7 @@ struct GnWork {
                           //                 phases: staging of the selected render rows, ray r at [r*D, r*D+cnt)
     float* sdf_samp;      // [total_rays*D]  SDF per ray sample (SDF_OUTSIDE outside the ball)
     float4* rrows;        // [total_rays*D]  per object: samples the FP16 forward pass left within refine_eps of a decision
-                          //                 threshold (| |s| - th | < eps): x,y,z,dest; re-evaluated by k_tc_refine
+                          //                 threshold (| |s| - th | < eps): x,y,z,dest; re-evaluated by k_tc_jacx<2>
     float refine_eps;     // 0: no second evaluation (FP32 mode, or switched off)
     int jac_wsplit;       // 1: the tcgen05 Jacobian kernel multiplies by hi(W) + lo(W) (two MMA passes per K chunk)
     int* ray_cnt;         // [total_rays]

@@ -465,7 +465,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         a.w.sdf_samp[dest] = sdf_y;
                         // The render term takes decisions at |s| = th (occupancy clamp, with_grad mask: loss.py:98-102).
                         // A sample the FP16-operand pass leaves within eps of a threshold is queued for the second,
-                        // FP32-grade evaluation (k_tc_refine), which overwrites sdf_samp[dest] before the ray scan.
+                        // FP32-grade evaluation (k_tc_jacx<2>), which overwrites sdf_samp[dest] before the ray scan.
                         if (a.w.refine_eps > 0.f && fabsf(fabsf(sdf_y) - a.w.prm.th) < a.w.refine_eps) {
                             const int slot = atomicAdd(&a.w.st[obj].rf_rows, 1);
                             const float4 pc = xyzs[r];
@@ -728,303 +728,25 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_tc_refine: second, FP32-grade forward evaluation of the few ray samples the FP16-operand pass left within
-// refine_eps of a decision threshold of the render term (| |s| - th | < eps; ~0.5-1 % of the evaluated samples).
+// k_tc_jacx: the decoder at FP32 grade on the tensor cores - both operands as hi + lo FP16 pairs (~22 significand bits).
 //
-// Both operands are carried as hi + lo FP16 pairs (~22 significand bits):
-//   * a tile holds REFINE_ROWS = 64 real rows, stacked to M = 128: tile row r < 64 is hi(a_r), row r + 64 is lo(a_r),
-//     so ONE M128 MMA multiplies both halves of the activations by a weight stage;
-//   * every K chunk is issued twice, against the hi(W) stage and the lo(W) stage (the same stage sequence packed
-//     from lo(W) = fp16(W - fp16(W)), LayerDesc::src_lo), accumulating in the same TMEM columns:
-//       lanes 0-63  : hi(a) (hi(W) + lo(W))      lanes 64-127 : lo(a) (hi(W) + lo(W))
-//   * the epilogue adds the two lane halves: warps q and q + 2 (TMEM lane quadrants of the hi and lo rows of the same
-//     32 real rows) swap 32-column slices through shared memory - each finalises half of the pair's 256 columns -
-//     then ReLU, split into hi / lo again and written to rows r and r + 64 of the next layer's A operand.
-// Cost per real row: 4 single-pass rows of tensor work; on < 1 % of the samples that is a few percent of the
-// forward kernel.  The extra blocks (bias, latent term, xyz columns; already hi/lo) multiply the hi rows only
-// (the lo rows of A_x are zero).
-// ------------------------------------------------------------------------------------------------
-struct RCfg {
-    static constexpr int NST = 3;
-    static constexpr int O_AX = A_BYTES;
-    static constexpr int O_ST = O_AX + AX_BYTES;
-    static constexpr int XB_WARP = 32 * 32 * 4;                     // one 32-column slice of 32 rows, FP32
-    static constexpr int O_XB = O_ST + NST * STAGE_BYTES;
-    static constexpr int O_W8 = O_XB + 8 * XB_WARP;
-    static constexpr int O_PART = O_W8 + 2048;
-    static constexpr int O_BAR = O_PART + 1024;
-    static constexpr int SMEM = O_BAR + 256 + 1024;
-};
-
-__global__ void __launch_bounds__(NT, 1) k_tc_refine(const __grid_constant__ TcArgs a) {
-    using C = RCfg;
-    constexpr int NST = C::NST;
-    extern __shared__ uint8_t smem_raw[];
-    const uint32_t raw = smem_u32(smem_raw);
-    const uint32_t sbase = (raw + 1023u) & ~1023u;
-    uint8_t* sm = smem_raw + (sbase - raw);
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const uint32_t sA = sbase, sAX = sbase + C::O_AX, sST = sbase + C::O_ST;
-    float* w8s = reinterpret_cast<float*>(sm + C::O_W8);
-    float* parts = reinterpret_cast<float*>(sm + C::O_PART);
-    const uint32_t bar0 = sbase + C::O_BAR;
-    auto bar_full = [&](int s) { return bar0 + 8u * s; };
-    auto bar_empty = [&](int s) { return bar0 + 8u * (NST + s); };
-    const uint32_t bar_aready = bar0 + 8u * (2 * NST), bar_dfull = bar0 + 8u * (2 * NST + 1);
-    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(sm + C::O_BAR + 8 * (2 * NST + 2));
-
-    if (tid == 0) {
-        for (int s = 0; s < NST; ++s) { mbar_init(bar_full(s), 1); mbar_init(bar_empty(s), 1); }
-        mbar_init(bar_aready, 8);
-        mbar_init(bar_dfull, 1);
-        fence_mbar_init();
-    }
-    if (warp == 9) {
-        tmem_alloc(smem_u32(const_cast<uint32_t*>(tmem_slot)), TMEM_COLS);
-        tmem_relinquish();
-    }
-    for (int i = tid; i < HID; i += NT) w8s[i] = __ldg(a.dec.w8 + i);
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem = *tmem_slot;
-    const int n_tiles = a.w.n_tiles[2];
-
-    if (warp == 8) {
-        // ===================== weight producer: every K chunk as a hi(W) stage followed by a lo(W) stage =====================
-        uint32_t s = 0, ph = 0;
-        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
-            const uint8_t* xo = a.xtra + (size_t)a.w.tile_obj[tb] * (2 * XTRA_BYTES);
-#pragma unroll 1
-            for (int li = 0; li < 8; ++li) {
-                const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[0][li]);
-                if (ld.xkind) {
-                    mbar_wait(bar_empty(s), ph ^ 1u);
-                    if (elect_one()) {
-                        const uint32_t bytes = (uint32_t)ld.n * 32u;
-                        mbar_expect_tx(bar_full(s), bytes);
-                        bulk_g2s(sST + s * STAGE_BYTES, (ld.xkind == 2 ? xo : a.blob) + ld.xsrc, bytes, bar_full(s));
-                    }
-                    __syncwarp();
-                    if (++s == NST) { s = 0; ph ^= 1u; }
-                }
-                const uint8_t* src_hi = a.blob + ld.src;
-                const uint8_t* src_lo = a.blob + ld.src_lo;
-                for (int n0 = 0; n0 < ld.n; n0 += 256) {
-                    const uint32_t bytes = (uint32_t)min(256, (int)ld.n - n0) * 64u;
-#pragma unroll 1
-                    for (int kc = 0; kc < 2 * ld.k32; ++kc) {
-                        mbar_wait(bar_empty(s), ph ^ 1u);
-                        if (elect_one()) {
-                            mbar_expect_tx(bar_full(s), bytes);
-                            bulk_g2s(sST + s * STAGE_BYTES, (kc & 1) ? src_lo : src_hi, bytes, bar_full(s));
-                        }
-                        __syncwarp();
-                        if (kc & 1) { src_hi += bytes; src_lo += bytes; }
-                        if (++s == NST) { s = 0; ph ^= 1u; }
-                    }
-                }
-            }
-        }
-    } else if (warp == 9) {
-        // ===================== MMA issuer =====================
-        uint32_t s = 0, ph = 0, aph = 0;
-        const uint64_t adesc0 = smem_desc(sA, 16, 1024, 2);
-        const uint64_t bdesc0 = smem_desc(sST, 16, 512, 4);
-        const uint64_t axdesc = smem_desc(sAX, 128, 256, 0);
-        const uint64_t bxdesc0 = smem_desc(sST, 128, 256, 0);
-        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
-#pragma unroll 1
-            for (int li = 0; li < 8; ++li) {
-                const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[0][li]);
-                mbar_wait(bar_aready, aph);
-                aph ^= 1u;
-                if (ld.xkind) {
-                    mbar_wait(bar_full(s), ph);
-                    tc_fence_after();
-                    if (elect_one()) {
-                        const uint64_t bx = bxdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
-                        for (int n0 = 0; n0 < ld.n; n0 += 256) {
-                            const int nn = min(256, (int)ld.n - n0);
-                            umma_f16(tmem + n0, axdesc, bx + (uint64_t)((n0 * 32) >> 4), idesc_f16(TILE_M, nn), 0u);
-                        }
-                        umma_commit(bar_empty(s));
-                    }
-                    __syncwarp();
-                    if (++s == NST) { s = 0; ph ^= 1u; }
-                }
-                for (int n0 = 0; n0 < ld.n; n0 += 256) {
-                    const uint32_t id = idesc_f16(TILE_M, min(256, (int)ld.n - n0));
-                    const uint32_t dcol = tmem + n0;
-#pragma unroll 1
-                    for (int k2 = 0; k2 < 2 * ld.k32; ++k2) {
-                        const int kc = k2 >> 1;
-                        mbar_wait(bar_full(s), ph);
-                        tc_fence_after();
-                        if (elect_one()) {
-                            const uint64_t ad = adesc0 + (uint64_t)((kc >> 1) * (A_BLK >> 4) + (kc & 1) * 4);
-                            const uint64_t bd = bdesc0 + (uint64_t)((s * STAGE_BYTES) >> 4);
-                            umma_f16(dcol, ad, bd, id, (ld.xkind == 0 && k2 == 0) ? 0u : 1u);
-                            umma_f16(dcol, ad + 2, bd + 2, id, 1u);
-                            umma_commit(bar_empty(s));
-                        }
-                        __syncwarp();
-                        if (++s == NST) { s = 0; ph ^= 1u; }
-                    }
-                }
-                if (elect_one()) umma_commit(bar_dfull);
-                __syncwarp();
-            }
-        }
-    } else {
-        // ===================== epilogue warps =====================
-        const int q = warp & 3, hc = warp >> 2;
-        const bool hi_thr = q < 2;                          // this warp's TMEM lanes hold hi rows (else the lo rows)
-        const int rr = (q & 1) * 32 + lane;                 // real row of the tile
-        const uint32_t trow = tmem + ((uint32_t)(q * 32) << 16);
-        const int rx = rr & 7;
-        const uint32_t arow_hi = sA + (uint32_t)(rr >> 3) * 1024u + (uint32_t)rx * 128u;
-        const uint32_t arow_lo = arow_hi + 8u * 1024u;      // tile row rr + 64
-        float* xb_out = reinterpret_cast<float*>(sm + C::O_XB + warp * C::XB_WARP);
-        const float* xb_in = reinterpret_cast<const float*>(sm + C::O_XB + (warp ^ 2) * C::XB_WARP);
-        const int pair_bar = 2 + (q & 1) + 2 * hc;          // named barrier of the warp pair (q, q ^ 2)
-        const int keep0 = hc * 256 + (hi_thr ? 0 : 128);    // columns this thread finalises
-        const int send0 = hc * 256 + (hi_thr ? 128 : 0);    // columns its partner finalises
-        uint32_t dph = 0;
-
-        auto signal_ready = [&]() {
-            tc_fence_before();
-            fence_proxy_async_smem();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_aready);
-        };
-        auto store32 = [&](uint32_t a_row, int col, const uint32_t* p) {
-            const uint32_t blk = a_row + (uint32_t)(col >> 6) * A_BLK;
-            const int cc0 = (col & 63) >> 3;
-#pragma unroll
-            for (int qq = 0; qq < 4; ++qq)
-                st_shared_v4(blk + (uint32_t)(((cc0 + qq) ^ rx) << 4), p[4 * qq], p[4 * qq + 1], p[4 * qq + 2], p[4 * qq + 3]);
-        };
-
-        for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
-            const int obj = a.w.tile_obj[tb], row0 = a.w.tile_row0[tb];
-            const int rows_valid = min(REFINE_ROWS, a.w.st[obj].rf_rows - row0);
-            bool valid = false;
-            int dest = -1;
-            if (hc == 0) {
-                const int trw = hi_thr ? rr : rr + 64;       // tile row whose A_x entry this thread writes
-                const uint32_t ax = sAX + (uint32_t)(trw >> 3) * 256u + (uint32_t)rx * 16u;
-                if (hi_thr) {
-                    float x = 0.f, y = 0.f, z = 0.f;
-                    valid = rr < rows_valid;
-                    if (valid) {
-                        const float4 v = a.w.rrows[(size_t)a.w.ray_off[obj] * a.w.prm.D + row0 + rr];
-                        x = v.x; y = v.y; z = v.z; dest = __float_as_int(v.w);
-                    }
-                    __half xh, xl, yh, yl, zh, zl;
-                    split_f16(x, xh, xl); split_f16(y, yh, yl); split_f16(z, zh, zl);
-                    const __half one = __float2half_rn(1.f), zero = __float2half_rn(0.f);
-                    const __half2 c0a = __halves2half2(one, one), c0b = __halves2half2(xh, yh), c0c = __halves2half2(zh, xl),
-                                  c0d = __halves2half2(yl, zl);
-                    const __half2 c1a = __halves2half2(xh, yh), c1b = __halves2half2(zh, zero), c1z = __halves2half2(zero, zero);
-                    st_shared_v4(ax, *reinterpret_cast<const uint32_t*>(&c0a), *reinterpret_cast<const uint32_t*>(&c0b),
-                                 *reinterpret_cast<const uint32_t*>(&c0c), *reinterpret_cast<const uint32_t*>(&c0d));
-                    st_shared_v4(ax + 128u, *reinterpret_cast<const uint32_t*>(&c1a), *reinterpret_cast<const uint32_t*>(&c1b),
-                                 *reinterpret_cast<const uint32_t*>(&c1z), *reinterpret_cast<const uint32_t*>(&c1z));
-                } else {                                     // lo rows take no bias / latent / xyz term
-                    st_shared_v4(ax, 0u, 0u, 0u, 0u);
-                    st_shared_v4(ax + 128u, 0u, 0u, 0u, 0u);
-                }
-            }
-            signal_ready();
-
-            for (int l = 0; l < 8; ++l) {
-                const bool last = (l == 7);
-                const int ncols = (l == 3) ? a.dec.h3p : HID;
-                mbar_wait(bar_dfull, dph);
-                dph ^= 1u;
-                tc_fence_after();
-                float part = 0.f;
-#pragma unroll 1
-                for (int i = 0; i < 4; ++i) {
-                    const int cs = send0 + 32 * i, ck = keep0 + 32 * i;
-                    const bool s_ok = cs < ncols, k_ok = ck < ncols;     // (warp-uniform; the partner sees the same two)
-                    uint32_t vs[32], vk[32];
-                    if (s_ok) tmem_ld32(trow + cs, vs);
-                    if (k_ok) tmem_ld32(trow + ck, vk);
-                    tmem_ld_wait();
-                    if (s_ok) {
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) xb_out[c * 32 + lane] = __uint_as_float(vs[c]);
-                    }
-                    named_bar_sync(pair_bar, 64);
-                    if (k_ok) {
-                        float f[32];
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) f[c] = fmaxf(__uint_as_float(vk[c]) + xb_in[c * 32 + lane], 0.f);
-                        if (!last) {
-                            uint32_t ph16[16], pl16[16];
-#pragma unroll
-                            for (int c = 0; c < 16; ++c) {
-                                const uint32_t h2 = pack_f16x2(f[2 * c], f[2 * c + 1]);
-                                const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&h2));
-                                ph16[c] = h2;
-                                pl16[c] = pack_f16x2(f[2 * c] - hf.x, f[2 * c + 1] - hf.y);
-                            }
-                            store32(arow_hi, ck, ph16);
-                            store32(arow_lo, ck, pl16);
-                        } else {
-                            const float4* w4 = reinterpret_cast<const float4*>(w8s + ck);
-#pragma unroll
-                            for (int c = 0; c < 8; ++c) {
-                                const float4 wv = w4[c];
-                                part = fmaf(f[4 * c + 0], wv.x, part);
-                                part = fmaf(f[4 * c + 1], wv.y, part);
-                                part = fmaf(f[4 * c + 2], wv.z, part);
-                                part = fmaf(f[4 * c + 3], wv.w, part);
-                            }
-                        }
-                    }
-                    named_bar_sync(pair_bar, 64);            // slice buffers reusable
-                }
-                if (!last) {
-                    signal_ready();
-                } else {
-                    parts[(hc * 2 + (hi_thr ? 0 : 1)) * REFINE_ROWS + rr] = part;
-                    tc_fence_before();
-                    named_bar_sync(1, EPI_THREADS);
-                    if (hc == 0 && hi_thr && valid) {
-                        const float y = tanhf(parts[rr] + parts[REFINE_ROWS + rr] + parts[2 * REFINE_ROWS + rr] +
-                                              parts[3 * REFINE_ROWS + rr] + a.dec.b8);
-                        a.w.sdf_samp[dest] = y;
-                    }
-                    named_bar_sync(1, EPI_THREADS);
-                }
-            }
-        }
-    }
-
-    tc_fence_before();
-    __syncthreads();
-    if (warp == 9) {
-        __syncwarp();
-        tc_fence_after();
-        tmem_dealloc(tmem, TMEM_COLS);
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// k_tc_jacx: SDF + Jacobian at FP32 grade on the tensor cores (DSPSLAM_MODE_TC_EXACT).
-//
-// The stacked hi/lo scheme of k_tc_refine carried through BOTH sweeps: a tile holds 64 real rows, tile row r is the hi
-// half and row r + 64 the lo half of the row's A operand (activations in the forward sweep, input gradients in the
-// backward sweep), every K chunk is issued against the hi(W) and the lo(W) stage image, and the epilogue warps q and
-// q + 2 add the two TMEM lane halves by swapping 32-column slices through shared memory.  The thread that finalises a
-// column keeps its ReLU sign bit and applies it to the same column of the backward sweep (the columns of D_l = g_l W_l
-// are the units of layer l - 1, so the ownership is the same in both directions).
-//   GN = false: rows from an xyz array -> sdf[n], jac[n][L + 3]          (dspslam_sdf_jac)
-//   GN = true : rows from the Jacobian work list (64-row tiles) -> per-tile J^T J | J^T r partials (dspslam_gn_*)
-// Cost: 4 single-pass rows of tensor work per real row and a heavier epilogue - about 4x the FP16 kernel per row.
+//   * a tile holds 64 real rows stacked to M = 128: tile row r < 64 is hi(a_r), row r + 64 is lo(a_r) (activations in
+//     the forward sweep, input gradients in the backward sweep), so ONE M128 MMA multiplies both halves by a weight stage;
+//   * every K chunk is issued twice, against the hi(W) stage and the lo(W) stage (the same stage sequence packed from
+//     lo(W) = fp16(W - fp16(W)), LayerDesc::src_lo), accumulating in the same TMEM columns:
+//       lanes 0-63 : hi(a) (hi(W) + lo(W))        lanes 64-127 : lo(a) (hi(W) + lo(W))
+//   * the epilogue adds the two lane halves (see the epilogue branch), applies ReLU (forward) or its mask (backward),
+//     splits into hi / lo again and writes rows r and r + 64 of the next A operand.  The warp that finalises a column
+//     keeps its ReLU sign bit for the backward sweep (the columns of D_l = g_l W_l are the units of layer l - 1, so the
+//     ownership is the same in both directions).
+//   * the extra blocks (bias, latent term, xyz columns; already hi/lo) multiply the hi rows only (zero A_x in the lo rows).
+//   XM = 0: rows from an xyz array -> sdf[n], jac[n][L + 3]                          (dspslam_sdf_jac, DSPSLAM_MODE_TC_EXACT)
+//   XM = 1: rows from the Jacobian work list (64-row tiles) -> J^T J | J^T r partials (dspslam_gn_*, DSPSLAM_MODE_TC_EXACT)
+//   XM = 2: forward sweep only over the ray samples the FP16-operand pass left within refine_eps of a decision
+//           threshold of the render term (| |s| - th | < eps, 0.5-1 % of the samples): the second evaluation of
+//           DSPSLAM_MODE_TC, written over sdf_samp[dest] before the per-ray scan
+// Cost: 4 single-pass rows of tensor work per real row and a heavier epilogue: 247 us per 64-row tile through both
+// sweeps against 156 us per 128-row tile of the FP16 kernel.
 // ------------------------------------------------------------------------------------------------
 struct XCfg {
     static constexpr int NST = 4;
@@ -1050,9 +772,11 @@ static_assert(XCfg::ROWS * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the ac
 #endif
 constexpr int XREP = (DSP_X_EXP == 3) ? 1 : 2;
 
-template <bool GN>
+template <int XM>   // 0: xyz array -> sdf + jac;  1: GN Jacobian rows -> J^T J partials;  2: GN second evaluation (forward only)
 __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArgs a) {
     using C = XCfg;
+    constexpr bool GN = (XM == 1), FWD = (XM == 2);
+    constexpr int NPROGX = FWD ? 1 : 2;
     constexpr int NST = C::NST;
     constexpr int ROWS = C::ROWS;
     extern __shared__ uint8_t smem_raw[];
@@ -1089,15 +813,15 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem = *tmem_slot;
-    const int n_tiles = GN ? a.w.n_tiles[1] : a.n_tiles;
+    const int n_tiles = FWD ? a.w.n_tiles[2] : (GN ? a.w.n_tiles[1] : a.n_tiles);
 
     if (warp == 8) {
         // ===================== weight producer: both programs, every K chunk as a hi(W) and a lo(W) stage =====================
         uint32_t s = 0, ph = 0;
         for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
-            const int obj = GN ? a.w.tile_obj[tb] : 0;
+            const int obj = (GN || FWD) ? a.w.tile_obj[tb] : 0;
             const uint8_t* xo = a.xtra + (size_t)obj * (2 * XTRA_BYTES);
-            for (int p = 0; p < 2; ++p) {
+            for (int p = 0; p < NPROGX; ++p) {
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
@@ -1138,7 +862,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
         const uint64_t axdesc = smem_desc(sAX, 128, 256, 0);
         const uint64_t bxdesc0 = smem_desc(sST, 128, 256, 0);
         for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
-            for (int p = 0; p < 2; ++p) {
+            for (int p = 0; p < NPROGX; ++p) {
 #pragma unroll 1
                 for (int li = 0; li < 8; ++li) {
                     const LayerDesc ld = *reinterpret_cast<const LayerDesc*>(&a.dec.tc_layers[p][li]);
@@ -1287,9 +1011,12 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
 
         for (int tb = blockIdx.x; tb < n_tiles; tb += gridDim.x) {
             // ---------------- tile rows ----------------
-            int obj = 0, row0 = 0, rows_valid = 0, M_obj = 0;
+            int obj = 0, row0 = 0, rows_valid = 0, M_obj = 0, dest = -1;
             size_t jb = 0;
-            if (GN) {
+            if (FWD) {
+                obj = a.w.tile_obj[tb]; row0 = a.w.tile_row0[tb];
+                rows_valid = min(ROWS, a.w.st[obj].rf_rows - row0);
+            } else if (GN) {
                 obj = a.w.tile_obj[tb]; row0 = a.w.tile_row0[tb];
                 M_obj = a.w.pts_off[obj + 1] - a.w.pts_off[obj];
                 const int K = a.w.prm.pose_only ? 0 : a.w.st[obj].K;
@@ -1307,7 +1034,10 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 if (hi_thr) {
                     float x = 0.f, y = 0.f, z = 0.f;
                     if (valid) {
-                        if (GN) {
+                        if (FWD) {
+                            const float4 v = a.w.rrows[(size_t)a.w.ray_off[obj] * a.w.prm.D + row0 + rr];
+                            x = v.x; y = v.y; z = v.z; dest = __float_as_int(v.w);
+                        } else if (GN) {
                             const float4 v = a.w.jrows[jb + row0 + rr];
                             x = v.x; y = v.y; z = v.z; coef = v.w;
                             if (row0 + rr >= M_obj) resid = a.w.jres[jb + row0 + rr];
@@ -1356,7 +1086,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                         m = (m << 1) | (f[c] > 0.f ? 1u : 0u);       // bit (31 - c) set <=> pre-activation c positive
                         f[c] = fmaxf(f[c], 0.f);
                     }
-                    mw[l][i] = m;
+                    if (!FWD) mw[l][i] = m;
                     if (!last) {
                         store_split(ck, f);
                     } else {                                  // layer 8 (1 x 512) folded into the last epilogue
@@ -1381,8 +1111,14 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 }
             }
 
+            if (FWD) {                                        // second evaluation: the SDF is all that is wanted
+                if (hc == 0 && hi_thr && valid) a.w.sdf_samp[dest] = sdf_y;
+                named_bar_sync(1, EPI_THREADS);
+                continue;
+            }
+
             // ---------------- backward (input-gradient) sweep ----------------
-            {
+            if (!FWD) {
                 // g7 = dy * w8 . relu'(a7) for this thread's 128 columns (no accumulator involved)
                 const float dyS = GSCALE * (1.f - sdf_y * sdf_y);
 #pragma unroll 1
@@ -1476,7 +1212,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                 tc_fence_before();
             }
 
-            if (!GN) {
+            if (XM == 0) {
                 named_bar_sync(1, EPI_THREADS);
                 const int in_dim = L + 3;
                 const int64_t g0 = (int64_t)tb * ROWS;
@@ -1486,7 +1222,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc_jacx(const __grid_constant__ TcArg
                     a.jac_out[(g0 + row) * in_dim + i] = jrow[row * JLD + i];
                 }
                 named_bar_sync(1, EPI_THREADS);
-            } else {
+            } else if (GN) {
                 // ---- residual weights, then J^T J / J^T r of the tile's 64 rows (optimizer.py:163-169) ----
                 const GnWork& w = a.w;
                 const ObjState& so = w.st[obj];
@@ -1679,7 +1415,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
             }
         }
     }
-    // ---- lo images of the forward program (k_tc_refine): same stage sequence from lo(W) = fp16(W - fp16(W)) ----
+    // ---- lo images of the forward program (k_tc_jacx): same stage sequence from lo(W) = fp16(W - fp16(W)) ----
     for (int l = 1; l < 8; ++l) {
         const int N = (l == 3) ? h3p : HID, K = (l == 4) ? h3p : HID;
         const int Nreal = (l == 3) ? h3 : HID, Kreal = (l == 4) ? h3 : HID;
@@ -1758,9 +1494,10 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
         e = cudaFuncSetAttribute(k_tc<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<MODE>::SMEM);
     TC_ATTR(0) TC_ATTR(1) TC_ATTR(2) TC_ATTR(3) TC_ATTR(4) TC_ATTR(5)
 #undef TC_ATTR
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_refine, cudaFuncAttributeMaxDynamicSharedMemorySize, RCfg::SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
+    static_assert(XCfg::SMEM <= 232448, "shared memory of the hi/lo kernels");
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_tc_jacx<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, XCfg::SMEM);
     if (e != cudaSuccess) {
         g_tc_err = cudaGetErrorString(e);
         cudaFree(dev);
@@ -1840,7 +1577,7 @@ int tc_launch_sdf_jac_exact(const DecoderDev& dec, int sm_count, const float* xy
     a.dec = dec; a.blob = dec.tc_blob; a.xtra = dec.tc_xtra1;
     a.xyz = xyz; a.n = n; a.out = sdf_out; a.jac_out = jac_out;
     a.n_tiles = (int)((n + XCfg::ROWS - 1) / XCfg::ROWS);
-    k_tc_jacx<false><<<std::min(std::min(a.n_tiles, sm_count), PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
+    k_tc_jacx<0><<<std::min(std::min(a.n_tiles, sm_count), PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
     return 2;
 }
 
@@ -1848,7 +1585,7 @@ int tc_launch_gn_jac_exact(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
-    k_tc_jacx<true><<<std::min(sm_count, PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
+    k_tc_jacx<1><<<std::min(sm_count, PARK_CTAS), NT, XCfg::SMEM, st>>>(a);
     return 1;
 }
 
@@ -1856,7 +1593,7 @@ int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st) {
     using namespace tc;
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w;
-    k_tc_refine<<<sm_count, NT, RCfg::SMEM, st>>>(a);
+    k_tc_jacx<2><<<sm_count, NT, XCfg::SMEM, st>>>(a);
     return 1;
 }
 

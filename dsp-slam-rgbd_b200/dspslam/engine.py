@@ -118,21 +118,19 @@ class Engine:
 
     # -- helpers ------------------------------------------------------------------------------
     def _staging(self, nbytes):
-        """Pinned host staging for one batch.  `cudaHostAlloc` costs about as much as a whole single-detection call,
-        so the buffers are kept per size class (powers of two) and per host thread, and handed out round-robin from
-        a ring of four: a batch stays valid while the next three are packed (callers that keep more JointBatch
-        objects alive at once pass pinned=False or pack into their own buffers)."""
+        """Pinned host staging for one batch.  Buffers are kept per size class (powers of two) and per host thread and
+        handed out alternately from a pair that is allocated together on the first use of the class, so that no call
+        after the first pays for `cudaHostAlloc`; a batch stays valid while the next one is packed (callers that keep
+        more JointBatch objects alive at once pass cached=False)."""
         import threading
         t = self.torch
         cls = 1 << max(12, int(nbytes - 1).bit_length())
         key = (threading.get_ident(), cls)
-        ring = self._pinned.setdefault(key, [[], 0])
-        if len(ring[0]) < 4:
-            ring[0].append(t.empty(cls, dtype=t.uint8, pin_memory=True))
-            buf = ring[0][-1]
-        else:
-            buf = ring[0][ring[1] % 4]
-            ring[1] += 1
+        ring = self._pinned.get(key)
+        if ring is None:
+            ring = self._pinned[key] = [[t.empty(cls, dtype=t.uint8, pin_memory=True) for _ in range(2)], 0]
+        buf = ring[0][ring[1] & 1]
+        ring[1] += 1
         return buf[:nbytes]
 
     def _stream(self):
