@@ -87,6 +87,24 @@ def test_code_len_32_queries_vs_oracle(mode):
     assert np.abs(g - orc.grid_sdf(od, code, 12, "lattice")).max() < tol
 
 
+def test_code_len_32_exact_mode_vs_oracle():
+    """The hi/lo kernel with a 32-long code: 35 Jacobian columns (the last step's N is 48), layer 3 emits 477 units."""
+    from dspslam.engine import Engine
+    from oracle import dspslam_oracle as orc
+    dec = _decoder32()
+    eng = Engine(dec)
+    od = orc.OracleDecoder(dec.state_dict())
+    rng = np.random.default_rng(12)
+    code = (0.3 * rng.normal(size=32)).astype(np.float32)
+    x = rng.uniform(-0.8, 0.8, size=(3001, 3)).astype(np.float32)
+    so, jo = od.sdf_jacobian(code, x)
+    s, j = eng.sdf_jac(code, x, mode="tc_exact")
+    assert j.shape == (3001, 35)
+    assert np.abs(s.cpu().numpy() - so).max() < 2e-5
+    err = np.abs(j.cpu().numpy() - jo)
+    assert (err.max(axis=1) > 1e-4).sum() <= 12 and np.median(err.max(axis=1)) < 2e-5
+
+
 def test_code_len_32_gn_step_vs_oracle():
     """One joint GN step (39 x 39 normal equations) in FP32 mode against the oracle; the tensor-core mode against
     the FP32 mode."""
@@ -118,9 +136,10 @@ def test_code_len_32_gn_step_vs_oracle():
         dt, ang, _ = synth.pose_errors(res.t_cam_obj[0], ref["t_cam_obj"])
         assert res.code.shape == (1, 32)
         assert dt < 1e-3 and ang < 0.05 and np.linalg.norm(res.code[0] - ref["code"]) < 1e-2 * max(1.0, np.linalg.norm(ref["code"]))
-        tc = eng.gn_joint([(T, pts, rays, depth, code)], _params(cfg, 1), mode="tc")
-        dt, ang, _ = synth.pose_errors(tc.t_cam_obj[0], res.t_cam_obj[0])
-        assert tc.status[0] == 0 and dt < 1e-2 and ang < 0.5
+        for m, tol in (("tc", 0.5), ("tc_exact", 0.05)):
+            tc = eng.gn_joint([(T, pts, rays, depth, code)], _params(cfg, 1), mode=m)
+            dt, ang, _ = synth.pose_errors(tc.t_cam_obj[0], res.t_cam_obj[0])
+            assert tc.status[0] == 0 and dt < 1e-2 and ang < tol, (m, dt, ang)
 
 
 @pytest.mark.parametrize("mode", ["fp32", "tc"])
