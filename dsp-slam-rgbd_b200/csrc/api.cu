@@ -60,6 +60,14 @@ struct dspslam_handle {
     cudaEvent_t done = nullptr;
     cudaStream_t last_stream = nullptr;
     bool has_done = false;
+    // second stream of the GN driver: the Jacobian tiles that hold surface rows only run here, beside the ray pipeline
+    // of the same iteration (gn_run); ev_state / ev_early order the two streams twice per iteration
+    cudaStream_t aux = nullptr;
+    cudaEvent_t ev_state = nullptr, ev_early = nullptr;
+    int early_min_tiles = 1 << 30;   // OFF by default: measured neutral (the second stream cannot be given a lower priority
+                                     // than a default-priority caller stream, so the early tiles run first instead of
+                                     // filling the gaps: 489-492 against 491-499 objects/s, profiles/r02_notes.md);
+                                     // environment variable DSPSLAM_JAC_EARLY=1 at handle creation switches it on (>= 16 tiles)
 };
 
 namespace {
@@ -171,7 +179,7 @@ int check_launch(dspslam_handle* h, int n_launch, const char* what) {
     return 0;
 }
 
-enum { PK_GN_FWD = 0, PK_GN_JAC = 1, PK_ROWS_FWD = 2, PK_ROWS_JAC = 3, PK_GN_REFINE = 4 };
+enum { PK_GN_FWD = 0, PK_GN_JAC = 1, PK_ROWS_FWD = 2, PK_ROWS_JAC = 3, PK_GN_REFINE = 4, PK_GN_JAC_EARLY = 5 };
 
 // records the start event of a profiled launch group; returns the pair index or -1
 int prof_begin(dspslam_handle* h, int kind, int64_t rows, cudaStream_t st) {
@@ -266,7 +274,11 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     if (e == cudaSuccess) e = cudaMemset(h->stats, 0, sizeof(unsigned long long) * 8);
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
     e = cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_state, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_early, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    if (const char* m = getenv("DSPSLAM_JAC_EARLY")) h->early_min_tiles = (atoi(m) != 0) ? 16 : (1 << 30);
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
@@ -285,6 +297,9 @@ void dspslam_destroy(dspslam_handle* h) {
         if (h->hblob) cudaFree(h->hblob);
         if (h->ws) cudaFree(h->ws);
         if (h->done) cudaEventDestroy(h->done);
+        if (h->ev_state) cudaEventDestroy(h->ev_state);
+        if (h->ev_early) cudaEventDestroy(h->ev_early);
+        if (h->aux) cudaStreamDestroy(h->aux);
         if (h->lat) cudaFree(h->lat);
         if (h->zeros) cudaFree(h->zeros);
         if (h->stats) cudaFree(h->stats);
@@ -466,7 +481,13 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_sres = c.take(sizeof(float) * (size_t)total_pts);
     const size_t o_tobj = c.take(sizeof(int) * max_tiles);
     const size_t o_trow = c.take(sizeof(int) * max_tiles);
-    const size_t o_ntl = c.take(sizeof(int) * 8);            // n_tiles[2] | done[2]
+    const size_t o_ntl = c.take(sizeof(int) * 8);            // n_tiles[4] | done[4]
+    // early Jacobian tiles: the k_tc<5> launches of the joint driver, batches with enough surface-only tiles
+    const size_t egroups_max = (size_t)max_pts / GROUP_ROWS;
+    const bool early = jac_tc && !exact && !prm.pose_only && h->aux && iters > 0 &&
+                       (size_t)B * egroups_max >= (size_t)h->early_min_tiles;
+    const size_t o_etobj = c.take(early ? sizeof(int) * ((size_t)B * egroups_max + 1) : 0);
+    const size_t o_etrow = c.take(early ? sizeof(int) * ((size_t)B * egroups_max + 1) : 0);
     const size_t o_toff = c.take(sizeof(int) * ((size_t)B + 1));
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
     const size_t o_xtra = c.take(mode != DSPSLAM_MODE_FP32 ? tc_xtra_bytes_per_object() * (size_t)B : 0);
@@ -498,6 +519,9 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.n_tiles = reinterpret_cast<int*>(base + o_ntl);
     w.done = reinterpret_cast<unsigned int*>(base + o_ntl) + 4;
     w.tile_off = reinterpret_cast<int*>(base + o_toff);
+    w.early = early ? 1 : 0;
+    w.etile_obj = reinterpret_cast<int*>(base + o_etobj);
+    w.etile_row0 = reinterpret_cast<int*>(base + o_etrow);
     w.tc = (mode != DSPSLAM_MODE_FP32) ? 1 : 0;
     w.partials = reinterpret_cast<float*>(base + o_part);
     w.stats = h->prof_on ? h->stats : nullptr;
@@ -512,6 +536,14 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     launch_gn_init(w, pose_in, code_in, h->dec.L, scale_in, st); ++nl;
     if (iters > 0) { launch_gn_prep(w, 0, st); ++nl; }
     for (int e = 0; e < iters; ++e) {
+        if (early) {        // state of iteration e is final (prep / solve are queued): the surface-only tiles start now
+            CK(cudaEventRecord(h->ev_state, st));
+            CK(cudaStreamWaitEvent(h->aux, h->ev_state, 0));
+            const int pe = prof_begin(h, PK_GN_JAC_EARLY, 0, h->aux);
+            nl += tc_launch_gn_jac(w, h->sm_count, 1, h->aux);
+            prof_end(h, pe, h->aux);
+            CK(cudaEventRecord(h->ev_early, h->aux));
+        }
         if (!prm.pose_only) {
             for (int ph = 0; ph < w.n_phases; ++ph) {      // front-to-back ray phases (k_gn_sample)
                 w.phase = ph;
@@ -533,8 +565,9 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
         const int pj = prof_begin(h, PK_GN_JAC, 0, st);
         if (!jac_tc) { launch_gn_jac_simt(w, st); ++nl; }
         else if (exact) nl += tc_launch_gn_jac_exact(w, h->sm_count, st);
-        else nl += tc_launch_gn_jac(w, h->sm_count, st);
+        else nl += tc_launch_gn_jac(w, h->sm_count, 0, st);
         prof_end(h, pj, st);
+        if (early) CK(cudaStreamWaitEvent(st, h->ev_early, 0));     // solve reads the early tiles' partials
         launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); ++nl;
     }
     launch_gn_final(w, pose_out, code_out, h->dec.L, scale_in, status_out, loss_out, st); ++nl;
@@ -720,8 +753,8 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
     std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     memset(out, 0, sizeof(*out));
-    double ms[5] = {0, 0, 0, 0, 0};
-    int64_t rows[5] = {0, 0, 0, 0, 0}, cnt[5] = {0, 0, 0, 0, 0};
+    double ms[6] = {0, 0, 0, 0, 0, 0};
+    int64_t rows[6] = {0, 0, 0, 0, 0, 0}, cnt[6] = {0, 0, 0, 0, 0, 0};
     for (size_t p = 0; p < h->prof_kind.size(); ++p) {
         CK(cudaEventSynchronize(h->prof_ev[2 * p + 1]));
         float t = 0.f;
@@ -737,7 +770,10 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
     CK(cudaMemset(h->stats, 0, sizeof(st)));
     h->prof_kind.clear();
     h->prof_rows.clear();
-    out->ms_gn_fwd = ms[PK_GN_FWD]; out->ms_gn_jac = ms[PK_GN_JAC];
+    // the early Jacobian launch shares the SMs with the ray pipeline on the other stream: its event time is the
+    // span it was resident for, an upper bound of its own SM time
+    out->ms_gn_fwd = ms[PK_GN_FWD]; out->ms_gn_jac = ms[PK_GN_JAC] + ms[PK_GN_JAC_EARLY];
+    out->ms_gn_jac_early = ms[PK_GN_JAC_EARLY];
     out->ms_rows_fwd = ms[PK_ROWS_FWD]; out->ms_rows_jac = ms[PK_ROWS_JAC];
     out->rows_gn_fwd = (int64_t)st[0]; out->rows_gn_jac = (int64_t)st[1]; out->rows_gn_inball = (int64_t)st[2];
     out->rows_fwd = rows[PK_ROWS_FWD]; out->rows_jac = rows[PK_ROWS_JAC];

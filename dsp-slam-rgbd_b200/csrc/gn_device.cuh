@@ -38,8 +38,15 @@ __device__ __forceinline__ void pack_extra_row(const DecoderDev& dec, int which,
     *reinterpret_cast<uint4*>(dst + 128) = *reinterpret_cast<const uint4*>(&h[8]);
 }
 
-// rows object b contributes to work list `which` (0: ray samples of the current phase, 1: Jacobian rows,
-// 2: ray samples queued for the second, FP32-grade evaluation - tiles of REFINE_ROWS rows)
+// rows of the object's Jacobian list that lie in tiles made of surface rows only: known as soon as the iteration's
+// state is, so their tiles run on a second stream beside the ray pipeline (GnWork::early)
+__device__ __forceinline__ int early_rows(const GnWork& w, int b) {
+    return w.early ? ((w.pts_off[b + 1] - w.pts_off[b]) / w.jac_rows) * w.jac_rows : 0;
+}
+
+// rows object b contributes to work list `which` (0: ray samples of the current phase, 1: Jacobian rows (behind the
+// early tiles), 2: ray samples queued for the second, FP32-grade evaluation - tiles of REFINE_ROWS rows, 3: the
+// early Jacobian tiles)
 // (volatile: the fields were written by other CTAs of the running kernel; an L1 line cached earlier by this CTA
 // could be stale)
 __device__ __forceinline__ int plan_rows(const GnWork& w, int which, int b) {
@@ -47,7 +54,8 @@ __device__ __forceinline__ int plan_rows(const GnWork& w, int which, int b) {
     if (st->status != 0) return 0;
     if (which == 0) return st->ph_rows[w.phase];
     if (which == 2) return st->rf_rows;
-    return (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : st->K);
+    if (which == 3) return early_rows(w, b);
+    return (w.pts_off[b + 1] - w.pts_off[b]) + (w.prm.pose_only ? 0 : st->K) - early_rows(w, b);
 }
 
 // Work list of the tcgen05 kernels: one entry (object, first row) per 128-row tile, objects in order.
@@ -59,7 +67,9 @@ static __device__ void plan_tiles(const GnWork& w, int which) {
     __shared__ int s_carry;
     __shared__ int s_off[1025];
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, nw = blockDim.x >> 5;
-    const int TR = (which == 2) ? REFINE_ROWS : (which == 1 ? w.jac_rows : GROUP_ROWS);      // rows per tile
+    const int TR = (which == 2) ? REFINE_ROWS : (which == 0 ? GROUP_ROWS : w.jac_rows);      // rows per tile
+    int* out_obj = (which == 3) ? w.etile_obj : w.tile_obj;
+    int* out_row0 = (which == 3) ? w.etile_row0 : w.tile_row0;
     if (tid == 0) s_carry = 0;
     __syncthreads();
     for (int base = 0; base < w.B; base += blockDim.x) {
@@ -102,8 +112,8 @@ static __device__ void plan_tiles(const GnWork& w, int which) {
     const int* off = (w.B <= 1024) ? s_off : w.tile_off;   // (global: written above by this CTA, fenced)
     for (int t = tid; t < total; t += blockDim.x) {
         const int b = find_segment(off, w.B, t);
-        w.tile_obj[t] = b;
-        w.tile_row0[t] = (t - off[b]) * TR;
+        out_obj[t] = b;
+        out_row0[t] = (t - off[b]) * TR + (which == 1 ? early_rows(w, b) : 0);
     }
 }
 

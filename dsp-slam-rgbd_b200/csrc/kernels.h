@@ -49,7 +49,11 @@ struct GnWork {
     // tcgen05 path work lists (filled by k_gn_plan_*)
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object
-    int* n_tiles;         // [3] number of forward / Jacobian / refinement tiles
+    int* n_tiles;         // [4] number of forward / Jacobian / refinement / early Jacobian tiles
+    int early;            // 1: the Jacobian tiles made of surface rows only have their own list (etile_*, n_tiles[3]),
+                          //    planned once, and run on the handle's second stream beside the ray pipeline
+    int* etile_obj;       // [B * ceil(max_pts / jac_rows)]
+    int* etile_row0;
     int* tile_off;        // [B+1] first tile of each object in the list being planned (scratch of plan_tiles)
     unsigned int* done;   // [2] "last CTA done" tickets of k_gn_sample / k_gn_ray_count (zero between launches)
     unsigned int* done_obj; // [B] per-object tickets of k_gn_ray_count

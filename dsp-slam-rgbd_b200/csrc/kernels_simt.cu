@@ -204,6 +204,8 @@ __global__ void k_gn_prep(GnWork w, int iter) {
     if (w.st[b].status == 0) prep_object(w, b, iter);       // (CTA-uniform)
     // pose-only runs have no ray kernels: the Jacobian tile list of the first iteration is planned here
     if (w.tc && w.prm.pose_only && last_cta_done(w.done + 1)) plan_tiles(w, 1);
+    // the early Jacobian tiles (surface rows only) do not change over the iterations: planned once
+    if (w.tc && w.early && iter == 0 && last_cta_done(w.done + 2)) plan_tiles(w, 3);
 }
 
 __global__ void k_gn_final(GnWork w, float* __restrict__ pose_out, float* __restrict__ code_out,

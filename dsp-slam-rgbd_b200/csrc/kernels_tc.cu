@@ -74,6 +74,7 @@ struct TcArgs {
     float* out;
     float* jac_out;
     int n_tiles;
+    int park_cta0;           // first per-CTA park block of this launch (two Jacobian launches may run side by side)
     int wsplit;              // bit l set: the forward sweep of the Jacobian variants issues every hidden K chunk of layer l
                              // against hi(W) and lo(W) (DSPSLAM_MODE_TC)
     // Gauss-Newton work lists
@@ -317,7 +318,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
         uint32_t mw[8][8];                                 // ReLU sign words of this thread's 256 columns, per layer
         const int L = a.dec.L;
         // layer-4 input gradients of row r wait here (written and read back by the hc == 1 thread of the row)
-        float* park = JAC ? a.dec.tc_park + (size_t)blockIdx.x * TILE_M * PARK_LD + r : nullptr;
+        float* park = JAC ? a.dec.tc_park + (size_t)(blockIdx.x + a.park_cta0) * TILE_M * PARK_LD + r : nullptr;
 #define PARK(c) park[(c) * TILE_M]
 
         auto signal_ready = [&]() {
@@ -1482,7 +1483,7 @@ int tc_pack_and_configure(DecoderDev& dec, const float* const* W, const float* c
 
     // device: [weight images | one extras record for the single-code entry points]
     const size_t wbytes = (B.bytes.size() + 255) & ~(size_t)255;
-    const size_t park_bytes = (size_t)PARK_CTAS * TILE_M * PARK_LD * sizeof(float);
+    const size_t park_bytes = (size_t)2 * PARK_CTAS * TILE_M * PARK_LD * sizeof(float);
     const size_t total = wbytes + 2 * XTRA_BYTES + park_bytes;
     uint8_t* dev = nullptr;
     cudaError_t e = cudaMalloc(&dev, total);
@@ -1597,10 +1598,14 @@ int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st) {
     return 1;
 }
 
-int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st) {
+int tc_launch_gn_jac(const GnWork& w, int sm_count, int early, cudaStream_t st) {
     using namespace tc;
     TcArgs a{};
     a.dec = w.dec; a.blob = w.dec.tc_blob; a.xtra = w.tc_xtra; a.w = w; a.wsplit = w.jac_wsplit;
+    if (early) {                                   // the early tile list, its own park blocks
+        a.w.tile_obj = w.etile_obj; a.w.tile_row0 = w.etile_row0; a.w.n_tiles = w.n_tiles + 2;   // [1] -> n_tiles[3]
+        a.park_cta0 = PARK_CTAS;
+    }
     launch_tc<5>(a, std::min(sm_count, PARK_CTAS), st);
     return 1;
 }

@@ -24,6 +24,6 @@ int tc_launch_gn_refine(const GnWork& w, int sm_count, cudaStream_t st);
 int tc_launch_sdf_jac_exact(const DecoderDev& dec, int sm_count, const float* xyz, int64_t n, const float* c0,
                             const float* c4, float* sdf_out, float* jac_out, cudaStream_t st);
 int tc_launch_gn_jac_exact(const GnWork& w, int sm_count, cudaStream_t st);
-int tc_launch_gn_jac(const GnWork& w, int sm_count, cudaStream_t st);
+int tc_launch_gn_jac(const GnWork& w, int sm_count, int early, cudaStream_t st);
 
 }  // namespace dsp

@@ -45,7 +45,7 @@ class Profile(C.Structure):
     _fields_ = [(n, C.c_double) for n in ("ms_gn_fwd", "ms_gn_jac", "ms_rows_fwd", "ms_rows_jac")] + \
                [(n, C.c_int64) for n in ("rows_gn_fwd", "rows_gn_jac", "rows_fwd", "rows_jac",
                                          "n_gn_fwd", "n_gn_jac", "n_rows_fwd", "n_rows_jac", "rows_gn_inball",
-                                         "rows_gn_refine", "n_gn_refine")] + [("ms_gn_refine", C.c_double)]
+                                         "rows_gn_refine", "n_gn_refine")] + [("ms_gn_refine", C.c_double), ("ms_gn_jac_early", C.c_double)]
 
 
 class FrameParams(C.Structure):

@@ -196,6 +196,8 @@ typedef struct {
     int64_t rows_gn_refine; /* ray samples evaluated a second time at FP32 grade (joint_params.refine_window)     */
     int64_t n_gn_refine;
     double ms_gn_refine;
+    double ms_gn_jac_early; /* part of ms_gn_jac: the Jacobian tiles of surface rows only, run on the handle's second
+                             * stream beside the ray pipeline (event span while sharing the SMs, an upper bound) */
 } dspslam_profile;
 int dspslam_profile_enable(dspslam_handle* h, int on);
 int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out);

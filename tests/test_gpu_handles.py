@@ -181,3 +181,32 @@ def test_one_handle_two_streams_two_threads(mode):
     for x in th:
         x.join()
     assert not errs, errs
+
+
+@pytest.mark.parametrize("mode", ["tc", "tc_fast"])
+def test_early_jacobian_tiles_on_second_stream_bit_identical(mode):
+    """Experiment knob DSPSLAM_JAC_EARLY=1: the Jacobian tiles made of surface rows only run on the handle's second
+    stream beside the ray pipeline of the same iteration (api.cu: gn_run; off by default, measured neutral).  Same
+    tiles, same partial slots, same summation order: the result is bit-identical to the single-stream schedule, run
+    after run."""
+    import os
+    from dspslam import synth
+    from dspslam.engine import Engine
+    dets = [synth.make_kitti_detection(40 + k, M=700 + 130 * k, n_bg=80) for k in range(5)]   # 5+6+7+8+9 = 35 early tiles
+    prm = _params(synth.kitti_config(), 4)
+    old = os.environ.get("DSPSLAM_JAC_EARLY")
+    try:
+        os.environ["DSPSLAM_JAC_EARLY"] = "0"
+        e0 = Engine(synth.load_wfit())
+        os.environ["DSPSLAM_JAC_EARLY"] = "1"
+        e1 = Engine(synth.load_wfit())
+        os.environ.pop("DSPSLAM_JAC_EARLY")
+    finally:
+        if old is not None:
+            os.environ["DSPSLAM_JAC_EARLY"] = old
+    a = e0.gn_joint(dets, prm, mode=mode, debug=True)
+    for _ in range(3):
+        b = e1.gn_joint(dets, prm, mode=mode, debug=True)
+        assert np.array_equal(a.t_cam_obj, b.t_cam_obj) and np.array_equal(a.code, b.code)
+        assert np.array_equal(a.dbg, b.dbg) and np.array_equal(a.status, b.status)
+    assert (a.status == 0).all()
