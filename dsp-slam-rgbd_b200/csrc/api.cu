@@ -490,6 +490,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     const size_t o_etrow = c.take(early ? sizeof(int) * ((size_t)B * egroups_max + 1) : 0);
     const size_t o_toff = c.take(sizeof(int) * ((size_t)B + 1));
     const size_t o_part = c.take(sizeof(float) * PART_STRIDE * (size_t)B * w.jgroups_max);
+    const size_t o_hred = c.take(sizeof(double) * PART_STRIDE * (size_t)B);
     const size_t o_xtra = c.take(mode != DSPSLAM_MODE_FP32 ? tc_xtra_bytes_per_object() * (size_t)B : 0);
     if (c.off > ((size_t)150 << 30)) return fail(DSPSLAM_E_NOMEM, "batch needs more than 150 GB of scratch: split it");
     int rc = ensure_ws(h, c.off, st);
@@ -524,6 +525,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
     w.etile_row0 = reinterpret_cast<int*>(base + o_etrow);
     w.tc = (mode != DSPSLAM_MODE_FP32) ? 1 : 0;
     w.partials = reinterpret_cast<float*>(base + o_part);
+    w.hred = reinterpret_cast<double*>(base + o_hred);
     w.stats = h->prof_on ? h->stats : nullptr;
     w.tc_xtra = reinterpret_cast<uint8_t*>(base + o_xtra);
 
@@ -568,7 +570,7 @@ static int gn_run(dspslam_handle* h, void* stream, int mode, const JointParamsDe
         else nl += tc_launch_gn_jac(w, h->sm_count, 0, st);
         prof_end(h, pj, st);
         if (early) CK(cudaStreamWaitEvent(st, h->ev_early, 0));     // solve reads the early tiles' partials
-        launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); ++nl;
+        launch_gn_solve(w, e, e == iters - 1, dbg_out, dbg_stride, st); nl += 2;
     }
     launch_gn_final(w, pose_out, code_out, h->dec.L, scale_in, status_out, loss_out, st); ++nl;
     return check_launch(h, nl, "dspslam_gn");

@@ -46,6 +46,7 @@ struct GnWork {
     uint8_t* active;      // [total_pts]     pose-only inlier flags
     float* sres;          // [total_pts]     last SDF residual per surface point
     float* partials;      // [B][jgroups_max][PART_STRIDE]
+    double* hred;         // [B][PART_STRIDE] the partials summed in tile order (k_gn_reduce -> k_gn_solve)
     // tcgen05 path work lists (filled by k_gn_plan_*)
     int* tile_obj;        // [max tiles] object of each 128-row tile
     int* tile_row0;       // [max tiles] first row of the tile inside the object

@@ -655,6 +655,45 @@ __global__ void __launch_bounds__(simt::NT, 1) k_gn_jac_simt(GnWork w) {
 // with w kept in the lower triangle and u in the (otherwise redundant) upper triangle, transposed.  b rides
 // along as row `dim` (its u lives in xs), which makes the forward substitution part of the same loop.
 // ---------------------------------------------------------------------------
+// Sum of the per-tile partials of every live object, element by element in tile order (FP64): what k_gn_solve used to
+// do with one CTA per object (45 % of its time waiting for 0.75 MB of loads per object at C2 size) spread over
+// REDUCE_SPLIT CTAs per object.  Same additions in the same order: H and b are bit-identical to the fused version.
+constexpr int REDUCE_SPLIT = 8;
+__global__ void __launch_bounds__(256) k_gn_reduce(GnWork w) {
+    const int b = blockIdx.y, tid = threadIdx.x;
+    const ObjState& s = w.st[b];
+    if (s.status != 0) return;
+    const int n = POSE + w.dec.L;
+    const int M = w.pts_off[b + 1] - w.pts_off[b];
+    const int K = w.prm.pose_only ? 0 : s.K;
+    const int ng = (M + K + w.jac_rows - 1) / w.jac_rows;
+    const int total = n * n + n, chunk = (total + REDUCE_SPLIT - 1) / REDUCE_SPLIT;
+    const int e0 = blockIdx.x * chunk, e1 = min(total, e0 + chunk);
+    const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
+    double* hred = w.hred + (size_t)b * PART_STRIDE;
+    for (int e = e0 + tid; e < e1; e += blockDim.x) {
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int g = 0;
+        for (; g + 16 <= ng; g += 16) {                     // 16 loads in flight, same order of additions as below
+            float v[16];
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = part[(size_t)(g + u) * PART_STRIDE + e];
+#pragma unroll
+            for (int u = 0; u < 16; u += 4) {
+                a0 += (double)v[u]; a1 += (double)v[u + 1]; a2 += (double)v[u + 2]; a3 += (double)v[u + 3];
+            }
+        }
+        for (; g + 4 <= ng; g += 4) {                       // fixed summation order: ((g0+g4+..)+(g1+..))+...
+            a0 += (double)part[(size_t)(g + 0) * PART_STRIDE + e];
+            a1 += (double)part[(size_t)(g + 1) * PART_STRIDE + e];
+            a2 += (double)part[(size_t)(g + 2) * PART_STRIDE + e];
+            a3 += (double)part[(size_t)(g + 3) * PART_STRIDE + e];
+        }
+        for (; g < ng; ++g) a0 += (double)part[(size_t)g * PART_STRIDE + e];
+        hred[e] = (a0 + a1) + (a2 + a3);                    // rows 0..n-1: H, row n: b
+    }
+}
+
 constexpr int SOLVE_NT = 512;
 
 __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int last_iter, float* __restrict__ dbg,
@@ -684,27 +723,9 @@ __global__ void __launch_bounds__(SOLVE_NT) k_gn_solve(GnWork w, int iter, int l
         }
         const int ng = (M + K + w.jac_rows - 1) / w.jac_rows;
         const float* part = w.partials + (size_t)b * w.jgroups_max * PART_STRIDE;
-        for (int e = tid; e < n * n + n; e += SOLVE_NT) {
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            int g = 0;
-            for (; g + 16 <= ng; g += 16) {                     // 16 loads in flight, same order of additions as below
-                float v[16];
-#pragma unroll
-                for (int u = 0; u < 16; ++u) v[u] = part[(size_t)(g + u) * PART_STRIDE + e];
-#pragma unroll
-                for (int u = 0; u < 16; u += 4) {
-                    a0 += (double)v[u]; a1 += (double)v[u + 1]; a2 += (double)v[u + 2]; a3 += (double)v[u + 3];
-                }
-            }
-            for (; g + 4 <= ng; g += 4) {                       // fixed summation order: ((g0+g4+..)+(g1+..))+...
-                a0 += (double)part[(size_t)(g + 0) * PART_STRIDE + e];
-                a1 += (double)part[(size_t)(g + 1) * PART_STRIDE + e];
-                a2 += (double)part[(size_t)(g + 2) * PART_STRIDE + e];
-                a3 += (double)part[(size_t)(g + 3) * PART_STRIDE + e];
-            }
-            for (; g < ng; ++g) a0 += (double)part[(size_t)g * PART_STRIDE + e];
-            Hs[e] = (a0 + a1) + (a2 + a3);                      // rows 0..n-1: H, row n: b
-        }
+        // the tile partials were summed (in tile order, FP64) by k_gn_reduce, spread over eight CTAs per object
+        const double* hred = w.hred + (size_t)b * PART_STRIDE;
+        for (int e = tid; e < n * n + n; e += SOLVE_NT) Hs[e] = hred[e];
         if (tid < 2) {
             float a = 0.f;
             for (int g = 0; g < ng; ++g) a += part[(size_t)g * PART_STRIDE + PART_LOSS + tid];
@@ -910,6 +931,7 @@ void launch_gn_jac_simt(const GnWork& w, cudaStream_t st) {
     k_gn_jac_simt<<<dim3(w.jgroups_max, w.B), simt::NT, simt_smem(), st>>>(w);
 }
 void launch_gn_solve(const GnWork& w, int iter, int last_iter, float* dbg, int dbg_stride, cudaStream_t st) {
+    k_gn_reduce<<<dim3(REDUCE_SPLIT, w.B), 256, 0, st>>>(w);
     k_gn_solve<<<w.B, SOLVE_NT, 0, st>>>(w, iter, last_iter, dbg, dbg_stride);
 }
 
