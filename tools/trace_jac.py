@@ -62,3 +62,19 @@ for c, g in M_:
 print("-- MMA issue windows (cycles; operands ready -> last MMA of the layer issued), median over tiles")
 for g in sorted(mdur):
     print("  %4d: %7.0f" % (g, np.median(mdur[g])))
+
+# per-stage log of the first tile's forward layer 1: 5000+k before the wait for the stage, 6000+k stage present, 7000+k
+# MMAs and commit issued
+st = {}
+for c, g in M_:
+    g = int(g)
+    if 5000 <= g < 8000:
+        st.setdefault(g % 1000, {})[g // 1000] = int(c)
+if st:
+    print("-- forward layer 1, first tile: per weight stage [wait for the stage | issue 2 MMAs + commit | loop period]")
+    prev = None
+    for k in sorted(st):
+        e = st[k]
+        if 5 in e and 6 in e and 7 in e:
+            print("  stage %2d: wait %5d  issue %5d  period %5s" % (k, e[6] - e[5], e[7] - e[6], "-" if prev is None else e[5] - prev))
+            prev = e[5]
