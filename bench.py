@@ -392,6 +392,7 @@ def ours_arm(args, rank, world, local_rank):
 def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ranks, sum_over_ranks):
     """The other BASELINE.json configs under the driver's clock, a few repetitions each (rank 0 returns the keys):
       c1  single KITTI-style car through `reconstruct_object` with host arrays (latency; rank 0 only)
+      c3  monocular detections (Redwood hyper-parameters, 48 samples, 20 iterations), 16 per rank
       c4  256^3 mesh grid, slabs over the ranks + overlapped NCCL all-gathers (the one collective of the design)
       c5  1 024 C1-shaped detections split contiguously over the ranks, H2D / D2H included
       parity  statistics of this mode against the reference-made vectors in tests/golden (tools/parity_stats.py)"""
@@ -436,6 +437,23 @@ def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ran
         out["c1"] = {"workload": "C1 single KITTI-style car: 250 surface pts + 450 rays x 50 samples, 10 GN iters, "
                                  "reconstruct_object() from host arrays",
                      "c1_ms_per_object": 1e3 * (time.perf_counter() - t0) / reps, "is_good": bool(o.is_good)}
+    barrier()
+    # ---- C3 mono: render-loss heavy, 20 iterations, 16 detections per rank ----
+    from reconstruct.optimizer import Optimizer as _Opt
+    opt3 = _Opt(dec, synth.redwood_config(iters=20, num_depth_samples=48), mode=args.mode, device=local_rank)
+    dets3 = [synth.make_mono_detection(rank * 16 + k) for k in range(16)]
+    for _ in range(2):
+        o3 = opt3.reconstruct_objects(dets3)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        o3 = opt3.reconstruct_objects(dets3)
+    torch.cuda.synchronize()
+    dt3 = max_over_ranks(time.perf_counter() - t0) / 3
+    good3 = int(sum_over_ranks(float(sum(1 for o in o3 if o.is_good))))
+    out["c3"] = {"workload": "C3 monocular (Redwood hyper-parameters): 16 detections/GPU x 256 surface pts + 1024 rays x 48 "
+                             "samples, 20 GN iters, reconstruct_objects() from host arrays",
+                 "objects_per_s": 16 * world / dt3, "ms_per_batch": 1e3 * dt3, "good": good3, "of": 16 * world}
     barrier()
     # ---- C4 grid + all-gather ----
     G = 256

@@ -7,6 +7,8 @@ oracle/make_goldens*.py) - the numbers behind north_star's ">= 95 % of reference
                state at iteration e against the reference's state at e + 1 (teacher forcing: the free-running
                trajectory is chaotic in the reference itself, tests/golden/noise_floor.json); a step is within
                tolerance when |dt| < 1 cm, rotation < 0.1 deg and |dcode| / max(|code|, 0.1) < 1e-2
+               (also bulk_c3.npz: 32 mono detections x 20 iterations; bulk_c2.npz: the 16 detections of the
+               benchmarked C2 batch itself, M = 2048 / N = 2248, x 10 iterations)
   objects      fraction of objects whose LAST step (the state the caller receives) is within tolerance, and
                fraction with every one of the 10 steps within tolerance
 
@@ -51,6 +53,8 @@ def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
     mono = "c3" in which
     cfg = synth.redwood_config() if mono else synth.kitti_config()
     make = synth.make_mono_detection if mono else synth.make_kitti_detection
+    if "c2" in which:                  # the benchmarked batch itself: M = 2048 surface points, 2248 rays
+        make = lambda k: synth.make_kitti_detection(k, M=2048, n_bg=200)
     ks = [k for k in range(min(n_objects, b["T_oc"].shape[0])) if b["is_good"][k]]
     dets = [make(k) for k in ks]
     for k, d in zip(ks, dets):      # the generator must still produce the inputs the reference ran on
@@ -96,6 +100,8 @@ def parity(eng, mode, n_objects=128):
         out["c1"] = step_stats(eng, mode, n_objects)
     if os.path.isfile(os.path.join(GOLD, "bulk_c3.npz")):
         out["c3"] = step_stats(eng, mode, 32, "bulk_c3.npz")
+    if os.path.isfile(os.path.join(GOLD, "bulk_c2.npz")):
+        out["c2"] = step_stats(eng, mode, 16, "bulk_c2.npz")
     return out
 
 
