@@ -766,8 +766,8 @@ struct XCfg {
 };
 static_assert(XCfg::ROWS * JLD * 4 <= A_BYTES, "Jacobian rows must fit in the activation tile");
 
-// timing experiments (wrong numerics on purpose; tools/bench_exact.py): -DDSP_X_EXP=1 no lane-half exchange,
-// 2 no activation stores, 3 no lo(W) pass
+// timing experiments (wrong numerics on purpose; tools/bench_exact.py): -DDSP_X_EXP=2 no activation stores,
+// 3 no lo(W) pass
 #ifndef DSP_X_EXP
 #define DSP_X_EXP 0
 #endif

@@ -1,5 +1,5 @@
 """Stand-alone timing of the exact SDF+Jacobian kernel (k_tc_jacx) and, with the `make -C csrc exp` variant libraries,
-of its timing experiments (wrong numerics on purpose: 1 no lane-half exchange, 2 no activation stores, 3 no lo(W) pass).
+of its timing experiments (wrong numerics on purpose: 2 no activation stores, 3 no lo(W) pass).
     python tools/bench_exact.py            # runs itself once per library found"""
 import os
 import subprocess
@@ -35,7 +35,7 @@ if len(sys.argv) > 1:
         out.append("%s n=%d: %.3f ms = %.1f us per tile-trip, %.1f Mquery/s" % (mode, n, ms, ms * 1e3 / 4, n / ms / 1e3))
     print(" | ".join(out), flush=True)
 else:
-    for lib in ["libdspslam_sm100.so"] + ["libdspslam_sm100_exp%d.so" % v for v in (1, 2, 3)]:
+    for lib in ["libdspslam_sm100.so"] + ["libdspslam_sm100_exp%d.so" % v for v in (2, 3)]:
         path = os.path.join(LIBDIR, lib)
         if os.path.isfile(path):
             subprocess.call([sys.executable, os.path.abspath(__file__), path])
