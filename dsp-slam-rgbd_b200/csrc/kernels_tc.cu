@@ -641,7 +641,9 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                         wrows[r] = wr;
                         rts[r] = rt;
                     }
+                    TRACE_E(1400);
                     named_bar_sync(1, EPI_THREADS);
+                    TRACE_E(1500);
                     // H is symmetric: 4x4 register blocks (bi <= bj) over the 128 rows, mirrored on the way out;
                     // the threads left over take J^T r.  ~23 instructions per row and block instead of 3 shared
                     // loads per multiply-add (the element-per-thread version was 27 % of the kernel).
@@ -674,6 +676,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
 #pragma unroll
                                 for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(a4[p], b4[q], acc[p][q]);
                         }
+                        TRACE_E(1550);
 #pragma unroll
                         for (int p = 0; p < 4; ++p)
 #pragma unroll
@@ -692,6 +695,7 @@ __global__ void __launch_bounds__(NT, 1) k_tc(const __grid_constant__ TcArgs a) 
                             part[n * n + i] = sacc;
                         }
                     }
+                    TRACE_E(1600);
                     if (hc == 0) {                                           // loss sums over the 128 rows
                         for (int o = 16; o > 0; o >>= 1) {
                             ls += __shfl_xor_sync(0xffffffffu, ls, o);

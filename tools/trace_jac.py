@@ -78,3 +78,17 @@ if st:
         if 5 in e and 6 in e and 7 in e:
             print("  stage %2d: wait %5d  issue %5d  period %5s" % (k, e[6] - e[5], e[7] - e[6], "-" if prev is None else e[5] - prev))
             prev = e[5]
+
+# last step of a tile: 100 accumulator complete, 1400 J row + weights written (warp 0), 1500 all rows there, 1600 warp 0's
+# 4x4 blocks summed, 2000 partials stored and loss sums done
+seq = [(int(c), int(g)) for c, g in E_ if int(g) in (100, 1400, 1500, 1550, 1600, 2000)]
+rows, cur = [], {}
+for c, g in seq:
+    cur[g] = c
+    if g == 2000 and len(cur) == 6:
+        rows.append([cur[1400] - cur[100], cur[1500] - cur[1400], cur[1550] - cur[1500], cur[1600] - cur[1550], cur[2000] - cur[1600]])
+        cur = {}
+if rows:
+    m = np.median(np.array(rows), axis=0)
+    print("-- last step (cycles, median over tiles): J row + weights %d | wait for the other warps %d | J^T J row loop %d | partial "
+          "stores %d | loss sums + barriers %d" % tuple(m))
