@@ -560,3 +560,50 @@ def test_degenerate_inputs_do_not_raise(wfit):
     assert out.shape == (2, 4, 4) and np.isnan(out[0]).all() and np.isfinite(out[1]).all()
     assert opt.estimate_poses_cam_obj([]).shape == (0, 4, 4)
     assert np.isnan(opt.compute_sdf_loss_objectpoint_zhjd(np.zeros((0, 3), np.float32), np.zeros(64, np.float32)))
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tc_exact", "tc"])
+def test_gn_fuzz_ragged_shapes_vs_oracle(mode, eng, odec):
+    """Seeded fuzz of the joint driver against the oracle: ragged surface / ray counts (down to a handful), depth-sample
+    counts from 16 to 64, hyper-parameters of all three configurations, warm-start codes, 2 GN iterations, as ONE
+    ragged batch.  FP32 and exact modes: pose within 1 mm / 0.02 deg of the oracle per object; default mode: the
+    north_star per-step tolerances on most objects."""
+    from oracle import dspslam_oracle as orc
+    from dspslam import synth
+    rng = np.random.default_rng(2026)
+    cases = []
+    for k in range(7):
+        D = int(rng.choice([16, 23, 32, 48, 50, 64]))
+        M = int(rng.integers(12, 700))
+        n_bg = int(rng.integers(0, 150))
+        kind = int(rng.integers(0, 3))
+        cases.append((k, D, M, n_bg, kind))
+    by_cfg = {}
+    for k, D, M, n_bg, kind in cases:
+        by_cfg.setdefault((D, kind), []).append((k, M, n_bg))
+    n_ok, n_all = 0, 0
+    for (D, kind), items in by_cfg.items():
+        cfg = [synth.kitti_config, synth.redwood_config, synth.freiburg_config][kind]()
+        cfg.optimizer.num_depth_samples = D
+        cfg.optimizer.joint_optim.num_iterations = 2
+        dets = []
+        for k, M, n_bg in items:
+            d = synth.make_kitti_detection(300 + k, M=M, n_bg=n_bg)
+            d["code"] = (0.05 * np.random.default_rng(k).normal(size=64)).astype(np.float32)
+            dets.append(d)
+        res = eng.gn_joint(dets, params(cfg, iters=2), mode=mode)
+        for i, d in enumerate(dets):
+            ref = orc.OracleOptimizer(odec, cfg).reconstruct_object(d["t_cam_obj"], d["pts"], d["rays"], d["depth"], code=d["code"])
+            assert bool(ref["is_good"]) == (res.status[i] == 0), (D, kind, items[i])
+            if not ref["is_good"]:
+                continue
+            dt, ang, _ = synth.pose_errors(res.t_cam_obj[i], ref["t_cam_obj"])
+            ec = np.linalg.norm(res.code[i] - ref["code"]) / max(np.linalg.norm(ref["code"]), 0.1)
+            n_all += 1
+            if mode == "tc":
+                n_ok += (dt < 1e-2 and ang < 0.1 and ec < 1e-2)
+                assert dt < 2e-2 and ang < 0.5 and ec < 0.1, (mode, D, kind, items[i], dt, ang, ec)
+            else:
+                n_ok += 1
+                assert dt < 1e-3 and ang < 0.02 and ec < 5e-3, (mode, D, kind, items[i], dt, ang, ec)
+    assert n_all >= 5 and n_ok >= n_all - 1
