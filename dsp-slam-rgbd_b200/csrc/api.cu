@@ -786,3 +786,68 @@ int dspslam_profile_read(dspslam_handle* h, dspslam_profile* out) {
 }
 
 }  // extern "C"
+
+// ---- dspslam_mean_sdf_noalloc: dspslam_mean_sdf for callers that must not allocate device memory ------------------
+// dspslam_mean_sdf parks the n decoder outputs in the handle's workspace in front of the reduction, and grows that
+// workspace with cudaMallocAsync when n exceeds what earlier calls needed.  This variant parks them in a fixed array
+// that is part of the library image instead, so the call itself never asks the driver for memory.
+namespace {
+
+// One copy per GPU that loads the library (1 MiB each, held until the process exits).  Shared by every handle and
+// every stream of that GPU; it keeps whatever the previous call left behind.  Nothing here has to start at zero: rows
+// [0, n) are overwritten by the decoder kernel before k_mean reads exactly those rows, so no clearing pass is needed.
+static __device__ __align__(256) float g_noalloc_rows[DSPSLAM_NOALLOC_MAX_ROWS];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_addr[NOALLOC_MAX_DEVICES] = {nullptr};   // device address of g_noalloc_rows on each GPU, looked up once
+
+// `g_noalloc_rows` in host code names a host-side shadow of the symbol, not the device array: handing it to a kernel
+// would fault (or, on a system where the GPU can reach host memory, quietly read and write the wrong place).  The
+// address a kernel can use is asked of the runtime, once per GPU, with that GPU current.
+int noalloc_rows_on(int device, float** out) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES) return fail(DSPSLAM_E_UNSUPPORTED, "device ordinal beyond the no-alloc table");
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_addr[device]) {
+        int cur = -1;
+        CK(cudaGetDevice(&cur));
+        if (cur != device) return fail(DSPSLAM_E_CUDA, "no-alloc set-up called with another device current");
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_rows));
+        if (!p) return fail(DSPSLAM_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_addr[device] = static_cast<float*>(p);
+    }
+    *out = g_noalloc_addr[device];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int dspslam_mean_sdf_noalloc(dspslam_handle* h, void* stream, int mode, const float* code, const float* xyz,
+                                        int64_t n, float* mean_out) {
+    if (!h || !mean_out || !code || !xyz || n <= 0) return fail(DSPSLAM_E_BADARG, "bad argument");
+    if (n > DSPSLAM_NOALLOC_MAX_ROWS) {
+        char buf[160];
+        snprintf(buf, sizeof buf, "dspslam_mean_sdf_noalloc: n = %lld exceeds DSPSLAM_NOALLOC_MAX_ROWS = %d "
+                 "(use dspslam_mean_sdf, which may allocate)", (long long)n, DSPSLAM_NOALLOC_MAX_ROWS);
+        return fail(DSPSLAM_E_BADARG, buf);
+    }
+    if (mode != DSPSLAM_MODE_FP32 && mode != DSPSLAM_MODE_TC && mode != DSPSLAM_MODE_TC_FAST && mode != DSPSLAM_MODE_TC_EXACT)
+        return fail(DSPSLAM_E_BADARG, "bad mode");
+    if (mode != DSPSLAM_MODE_FP32 && !h->tc_ready) return fail(DSPSLAM_E_UNSUPPORTED, "tcgen05 path unavailable: " + h->tc_why);
+    std::lock_guard<std::mutex> lk(h->mu);
+    DeviceGuard g(h->device);
+    float* rows = nullptr;
+    int rc = noalloc_rows_on(h->device, &rows);   // first call on this GPU: symbol look-up (before any stream capture)
+    if (rc) return rc;
+    StreamOrder so(h, stream);
+    // same launches as dspslam_mean_sdf, minus the profiling events (their pool grows on demand)
+    float* c0 = h->lat;
+    float* c4 = h->lat + HID;
+    launch_latent_bias(h->dec, code, 1, h->dec.L, c0, c4, S(stream));
+    int nl = 2;
+    if (mode == DSPSLAM_MODE_FP32) launch_sdf_rows_simt(h->dec, xyz, n, c0, c4, rows, S(stream));
+    else nl = 1 + tc_launch_sdf_rows(h->dec, h->sm_count, xyz, n, 0, 0, 0, c0, c4, rows, S(stream));
+    launch_mean(rows, n, mean_out, S(stream));
+    return check_launch(h, nl + 1, "dspslam_mean_sdf_noalloc");
+}

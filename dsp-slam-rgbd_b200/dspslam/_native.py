@@ -22,8 +22,9 @@ EXPORTS = [
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
     "dspslam_marching_cubes", "dspslam_frame_build_kitti", "dspslam_frame_build_mono",
-    "dspslam_pg_from_matrices", "dspslam_pg_linearize", "dspslam_pg_oplus",
+    "dspslam_pg_from_matrices", "dspslam_pg_linearize", "dspslam_pg_oplus", "dspslam_mean_sdf_noalloc",
 ]
+NOALLOC_MAX_ROWS = 262144
 FRAME_INFO = 8
 FRAME_MAX_DETS = 256
 FRAME_MAX_MASKS = 256
@@ -94,6 +95,8 @@ def lib():
     L.dspslam_sdf_jac.argtypes = [vp, vp, C.c_int, fp, fp, i64, fp, fp]
     L.dspslam_mean_sdf.restype = C.c_int
     L.dspslam_mean_sdf.argtypes = [vp, vp, C.c_int, fp, fp, i64, fp]
+    L.dspslam_mean_sdf_noalloc.restype = C.c_int
+    L.dspslam_mean_sdf_noalloc.argtypes = [vp, vp, C.c_int, fp, fp, i64, fp]
     L.dspslam_grid_sdf.restype = C.c_int
     L.dspslam_grid_sdf.argtypes = [vp, vp, C.c_int, fp, C.c_int, i64, i64, C.c_int, fp]
     L.dspslam_marching_cubes.restype = C.c_int

@@ -116,6 +116,26 @@ int dspslam_sdf_jac(dspslam_handle* h, void* stream, int mode, const float* code
 int dspslam_mean_sdf(dspslam_handle* h, void* stream, int mode, const float* code,
                      const float* xyz, int64_t n, float* mean_out);
 
+/* dspslam_mean_sdf for callers that are not allowed to allocate device memory.  No counterpart in the reference (its
+ * PyTorch path allocates freely); it exists for hosts of this library that cannot: a tracking or mapping thread that
+ * runs under a fixed memory budget handed out at start-up, a process whose GPU memory is owned by another allocator
+ * (a memory pool or an arena the library must not bypass), or a real-time loop in which a driver allocation - a call
+ * that can block and synchronise the device - is not acceptable.  dspslam_mean_sdf parks the n decoder outputs in a
+ * workspace that it grows with cudaMallocAsync on demand; this variant parks them in a fixed array inside the
+ * library image and makes no cudaMalloc / cudaFree / allocating library call at all.
+ *   - limit: n <= DSPSLAM_NOALLOC_MAX_ROWS; a larger n is refused with DSPSLAM_E_BADARG and a message naming the limit.
+ *     The array costs DSPSLAM_NOALLOC_MAX_ROWS * 4 bytes = 1 MiB on every GPU the library is loaded on, until exit.
+ *   - the first call on each GPU looks the array's device address up (cudaGetSymbolAddress, with that GPU current);
+ *     make that first call during set-up, before any stream capture begins.
+ *   - the array is shared by all handles and streams of a GPU and keeps the previous call's contents (nothing needs
+ *     clearing: the rows a call reads are the rows it has just written).  Calls on ONE handle are ordered as for every
+ *     other entry point; calls on DIFFERENT handles of the same GPU that overlap on the device race on the array -
+ *     put them on one stream or order them with events.
+ * Same arithmetic, same result as dspslam_mean_sdf (bit-identical on the same mode). */
+#define DSPSLAM_NOALLOC_MAX_ROWS 262144
+int dspslam_mean_sdf_noalloc(dspslam_handle* h, void* stream, int mode, const float* code,
+                             const float* xyz, int64_t n, float* mean_out);
+
 /* SDF over linear grid indices [i0, i1) of a G^3 grid over [-1,1]^3 (x slowest, z fastest);
  * out[i - i0].  coord_mode: DSPSLAM_GRID_REFERENCE_SHEAR reproduces the reference's
  * true-division grid, DSPSLAM_GRID_LATTICE the regular lattice. */
