@@ -60,17 +60,41 @@ def make_dets(rank, n=OBJ_PER_RANK):
     return [synth.make_kitti_detection(rank * OBJ_PER_RANK + k, M=M_PTS, n_bg=N_BG) for k in range(n)]
 
 
-def traffic_of(kernel):
-    """dram bytes per launch of `kernel` from the committed ncu capture, or None."""
-    try:
-        with open(os.path.join(ROOT, "profiles", "r02_traffic.json")) as f:
-            k = json.load(f)["kernels"]
-        for name, v in k.items():
-            if kernel in name:
-                return int(v["traffic_bytes"])
-    except (OSError, KeyError, ValueError):
-        pass
-    return None
+KERNEL_SOURCES = ("kernels_tc.cu", "kernels_tc.h", "tc_ptx.cuh", "common.cuh", "gn_device.cuh")
+
+
+def kernel_src_sha16():
+    """sha256 (first 16 hex) over the sources of the tcgen05 kernels: ties a committed ncu capture to a build."""
+    import hashlib
+    h = hashlib.sha256()
+    for n in KERNEL_SOURCES:
+        with open(os.path.join(ROOT, "dsp-slam-rgbd_b200", "csrc", n), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
+def traffic_of(kernel, with_source=False):
+    """dram bytes per launch of `kernel` from the newest committed ncu capture (profiles/r*_traffic.json,
+    tools/ncu_traffic.py) that was taken on THESE kernel sources and THIS workload; None when the only captures are of
+    another build (a stale number next to live timings is worse than null)."""
+    import glob
+    res = (None, None)
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")), reverse=True):
+        try:
+            with open(path) as f:
+                j = json.load(f)
+            if j.get("kernel_src_sha16") != kernel_src_sha16() or j.get("workload") != workload_desc():
+                continue
+            for name, v in j["kernels"].items():
+                if kernel in name:
+                    res = (int(v["traffic_bytes"]), "%s (dram__bytes_read.sum + dram__bytes_write.sum, %s)"
+                           % (os.path.relpath(path, ROOT), j.get("source")))
+                    break
+        except (OSError, KeyError, ValueError):
+            continue
+        if res[0] is not None:
+            break
+    return res if with_source else res[0]
 
 
 def peaks():
@@ -210,7 +234,8 @@ def reference_arm(args, rank, world):
     what = ("the UNMODIFIED reference (oracle/_ref = verbatim reconstruct/optimizer.py:90-205 + loss*.py + deep_sdf, torch CPU FP32)"
             if kind == "reference" else "numpy oracle port of reconstruct/optimizer.py (oracle/_ref absent)")
     sample = ("%d steps, each ONE C2 detection (M=%d, N=%d, D=%d) x all %d GN iterations; %.2f s of CPU work per step "
-              "(min %.2f, max %.2f); warm-up = %d C1-sized detection(s), untimed"
+              "(min %.2f, max %.2f); warm-up = %d C1-sized detection(s), untimed; decoder parameters frozen "
+              "(requires_grad False, oracle/ref_runner.py - less backward work than the stock script, i.e. in the reference's favour)"
               % (K, M_PTS, M_PTS + N_BG, D_SAMPLES, ITERS, mean_s, min(secs), max(secs), 1 if args.warmup > 0 else 0))
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "objects/s", "n_gpus": args.gpus,
             "steps": K, "warmup": args.warmup, "ms_per_step": 1e3 * mean_s, "objects_per_step": 1,
@@ -274,8 +299,7 @@ def ours_arm(args, rank, world, local_rank):
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     l0 = eng.launches
     barrier()
-    if rank == 0:
-        sampler.start()
+    sampler.start()                                      # every rank samples its own board (per_rank below)
     t_wall0 = time.time()
     for a, b in ev:
         flush.fill_(1)                                   # L2 flush between steps (untimed)
@@ -284,10 +308,19 @@ def ours_arm(args, rank, world, local_rank):
         b.record()
     barrier()
     t_wall1 = time.time()
-    clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    clocks = sampler.stop(t_wall0, t_wall1)
     launches = eng.launches - l0
     step_ms = [a.elapsed_time(b) for a, b in ev]
     dev_ms = max_over_ranks(float(np.sum(step_ms)))
+    # per-rank step time, SM clock and board power: what the max over ranks is made of (weak-scaling attribution)
+    mine = [float(np.mean(step_ms)), float((clocks or {}).get("sm_mhz") or 0.0), float((clocks or {}).get("power_w_mean") or 0.0),
+            float(len((clocks or {}).get("reasons") or []))]
+    if world > 1:
+        tl = [torch.zeros(4, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(tl, torch.tensor(mine, dtype=torch.float64, device=dev))
+        per_rank = [t.tolist() for t in tl]
+    else:
+        per_rank = [mine]
     prof = eng.profile_read()
     eng.profile_enable(False)
 
@@ -333,13 +366,16 @@ def ours_arm(args, rank, world, local_rank):
         "roofline": {"bound": "tensor", "kernel": "forward-only decoder over in-ball ray samples (GN render term)",
                      "achieved": fwd_tf, "peak": pk["tflops"], "unit": "TFLOP/s", "frac": fwd_tf / pk["tflops"],
                      # DRAM bytes of one forward launch (read + write) from the committed `ncu --set full` capture of this
-                     # command (tools/ncu_traffic.py -> profiles/r02_traffic.json); null when the file is missing
+                     # command (tools/ncu_traffic.py -> profiles/rNN_traffic.json); null unless a capture of this build exists
                      "traffic": traffic_of("k_tc<3>") if args.mode != "fp32" else None,
-                     "traffic_source": "profiles/r02_traffic.json (dram__bytes_read.sum + dram__bytes_write.sum, "
-                                       "profiles/r02_prof_bench_k_tc.ncu-rep)",
+                     "traffic_source": (traffic_of("k_tc<3>", True)[1] or "no ncu capture of this build and workload under "
+                                        "profiles/ (kernel_src_sha16 %s)" % kernel_src_sha16()),
                      "peak_source": pk["src"],
                      "avg_launch_ms": prof["ms_gn_fwd"] / max(1, prof["n_gn_fwd"]),
                      "rows_per_launch": prof["rows_gn_fwd"] / max(1, prof["n_gn_fwd"]),
+                     "launch_note": "two launches per GN iteration are averaged here: the large phase-0 launch (all rays, "
+                                    "~2 ms) and the small phase-1 launch (rays still alive, ~0.06 ms); achieved = all rows "
+                                    "/ all launch time",
                      "share_of_step": prof["ms_gn_fwd"] / max(1e-9, float(np.sum(step_ms))),
                      "rows_evaluated": int(prof["rows_gn_fwd"]), "rows_in_ball": int(prof["rows_gn_inball"]),
                      "note": "rows_evaluated < rows_in_ball: rays stop at their first sample with sdf <= -th "
@@ -384,6 +420,36 @@ def ours_arm(args, rank, world, local_rank):
                 line["reference_gpu"] = {"unavailable": str(ex)[-300:]}
     else:
         line["cpu_baseline"] = None
+    # compact, numbers-only digest as the LAST key of the line: a record that keeps only the tail of the line still
+    # holds every configuration (c1..c5), the operating points, the per-rank split and the parity fractions
+    r3 = lambda x: None if x is None else round(float(x), 3)
+    par = extra.get("parity") or {}
+    frac = lambda k, f: r3((par.get(k) or {}).get(f))
+    tail = {"n_gpus": world, "mode": args.mode, "objects_per_s": r3(value), "e2e_objects_per_s": r3(line["e2e"]["value"]),
+            "wsplit_mask": int(eng.lib.dspslam_query(eng._h, 0)), "jac_early": int(eng.lib.dspslam_query(eng._h, 1)),
+            "per_rank": {"ms_per_step": [r3(r[0]) for r in per_rank], "sm_mhz": [r3(r[1]) for r in per_rank],
+                         "power_w": [r3(r[2]) for r in per_rank], "throttle_reasons": [int(r[3]) for r in per_rank]}}
+    if "c1" in extra:
+        tail["c1_ms"] = r3(extra["c1"]["c1_ms_per_object"])
+    if "c3" in extra:
+        tail["c3_objects_per_s"] = r3(extra["c3"]["objects_per_s"])
+    if "c4" in extra:
+        c4 = extra["c4"]
+        tail["c4"] = {k: r3(c4[k]) for k in ("ms_grid", "ms_slab_compute", "ms_allgather_exposed", "ms_allgather_alone",
+                                             "tflops", "hbm_gbs_algorithmic")}
+        tail["c4"]["pieces"] = c4["pieces"]
+    if "c5" in extra:
+        tail["c5_objects_per_s"] = r3(extra["c5"]["objects_per_s"])
+    if "modes_objects_per_s_per_gpu" in extra:
+        tail["modes"] = {k: r3(v) for k, v in extra["modes_objects_per_s_per_gpu"].items() if k != "note"}
+    if par and "error" not in par:
+        tail["parity"] = {"jac_rows": frac("jacobian", "rows_within"), "c1_steps": frac("c1", "steps_within"),
+                          "c1_last": frac("c1", "objects_last_step_within"), "c1_free_run": frac("c1_free_run", "within"),
+                          "heldout_steps": frac("c1_heldout", "steps_within"),
+                          "heldout_last": frac("c1_heldout", "objects_last_step_within"),
+                          "heldout_free_run": frac("c1_heldout_free_run", "within"),
+                          "c2_steps": frac("c2", "steps_within"), "c3_steps": frac("c3", "steps_within")}
+    line["tail"] = tail
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -487,7 +553,11 @@ def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ran
                              "overlapping the next piece's kernel",
                  "ms_grid": ms_tot, "ms_slab_compute": ms_comp, "ms_allgather_exposed": ms_expo,
                  "ms_allgather_alone": ms_ag, "ms_allgather_hidden": max(0.0, ms_ag - ms_expo), "pieces": tm.get("pieces"),
-                 "mquery_per_s": G ** 3 / ms_tot / 1e3, "tflops": G ** 3 * FLOP_FWD / ms_tot / 1e9, "checksum": checksum}
+                 "mquery_per_s": G ** 3 / ms_tot / 1e3, "tflops": G ** 3 * FLOP_FWD / ms_tot / 1e9,
+                 # algorithmic HBM bytes of the grid kernel: 4 B written per voxel (coordinates are generated from the
+                 # linear index, nothing is read per row) + the 7.4 MB FP16 weight image once per launch - the kernel is
+                 # tensor-bound by three orders of magnitude, the figure is here because north_star asks for it
+                 "hbm_gbs_algorithmic": (4.0 * G ** 3 / world + 7.4e6) / (ms_comp * 1e-3) / 1e9, "checksum": checksum}
     del vol
     # ---- C5 sweep ----
     n_total = 1024

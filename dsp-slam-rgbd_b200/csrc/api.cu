@@ -228,6 +228,15 @@ extern "C" {
 int dspslam_abi_version(void) { return DSPSLAM_ABI_VERSION; }
 const char* dspslam_last_error(void) { return g_err.c_str(); }
 int64_t dspslam_launch_count(const dspslam_handle* h) { return h ? h->launches : 0; }
+int dspslam_query(const dspslam_handle* h, int what) {
+    if (!h) { g_err = "null handle"; return -1; }
+    switch (what) {
+        case DSPSLAM_Q_WSPLIT_MASK: return h->wsplit_mask;
+        case DSPSLAM_Q_JAC_EARLY: return h->early_min_tiles < (1 << 30) ? 1 : 0;
+        case DSPSLAM_Q_DEVICE: return h->device;
+        default: g_err = "unknown query"; return -1;
+    }
+}
 int dspslam_mode_available(const dspslam_handle* h, int mode) {
     if (!h) { g_err = "null handle"; return 0; }
     if (mode == DSPSLAM_MODE_FP32) return 1;
@@ -278,11 +287,20 @@ int dspslam_create(const dspslam_decoder_desc* desc, const float* const* W_host,
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->ev_early, cudaEventDisableTiming);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&h->aux, cudaStreamNonBlocking);
     if (e != cudaSuccess) { dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, cudaGetErrorString(e)); }
+    // experiment knobs (include/dspslam.h, "Environment variables"); read back with dspslam_query
     if (const char* m = getenv("DSPSLAM_JAC_EARLY")) h->early_min_tiles = (atoi(m) != 0) ? 16 : (1 << 30);
     rc = tc_pack_and_configure(h->dec, W_host, b_host, &h->hblob);
     if (rc > 1) { std::string m = tc_last_error(); dspslam_destroy(h); return fail(DSPSLAM_E_CUDA, "tcgen05 path setup: " + m); }
     h->tc_ready = (rc == 0);
-    if (const char* m = getenv("DSPSLAM_WSPLIT_MASK")) h->wsplit_mask = (int)strtol(m, nullptr, 0) & 0xFE;
+    if (const char* m = getenv("DSPSLAM_WSPLIT_MASK")) {
+        char* end = nullptr;
+        const long v = strtol(m, &end, 0);
+        if (end == m || *end != '\0' || v < 0 || v > 0xFF) {     // a typo must not silently select the tc_fast arithmetic
+            dspslam_destroy(h);
+            return fail(DSPSLAM_E_BADARG, std::string("DSPSLAM_WSPLIT_MASK is not an integer in 0..255: '") + m + "'");
+        }
+        h->wsplit_mask = (int)v & 0xFE;
+    }
     if (rc == 1) h->tc_why = tc_last_error();
     *out = h;
     return 0;

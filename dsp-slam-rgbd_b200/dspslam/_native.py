@@ -22,8 +22,9 @@ EXPORTS = [
     "dspslam_destroy", "dspslam_sdf", "dspslam_sdf_jac", "dspslam_mean_sdf", "dspslam_grid_sdf",
     "dspslam_gn_joint", "dspslam_gn_pose_only", "dspslam_profile_enable", "dspslam_profile_read",
     "dspslam_marching_cubes", "dspslam_frame_build_kitti", "dspslam_frame_build_mono",
-    "dspslam_pg_from_matrices", "dspslam_pg_linearize", "dspslam_pg_oplus", "dspslam_mean_sdf_noalloc",
+    "dspslam_pg_from_matrices", "dspslam_pg_linearize", "dspslam_pg_oplus", "dspslam_mean_sdf_noalloc", "dspslam_query",
 ]
+Q_WSPLIT_MASK, Q_JAC_EARLY, Q_DEVICE = 0, 1, 2
 NOALLOC_MAX_ROWS = 262144
 FRAME_INFO = 8
 FRAME_MAX_DETS = 256
@@ -82,6 +83,8 @@ def lib():
     L.dspslam_last_error.restype = C.c_char_p
     L.dspslam_launch_count.restype = i64
     L.dspslam_launch_count.argtypes = [vp]
+    L.dspslam_query.restype = C.c_int
+    L.dspslam_query.argtypes = [vp, C.c_int]
     L.dspslam_mode_available.restype = C.c_int
     L.dspslam_mode_available.argtypes = [vp, C.c_int]
     L.dspslam_create.restype = C.c_int

@@ -22,14 +22,22 @@ _MODES = {"fp32": N.MODE_FP32, "tc": N.MODE_TC, N.MODE_FP32: N.MODE_FP32, N.MODE
 _LIVE = []        # weak references to the engines constructed in this process, oldest first
 
 
-def last_engine():
-    """The most recently constructed Engine of the process that is still alive, or None (callers that are handed
-    neither a decoder nor a config - `convert_sdf_voxels_to_mesh`, the sequence classes - borrow it)."""
+def last_engine(device=None):
+    """The most recently constructed live Engine ON `device` (an index; default: the current CUDA device), or None.
+    Callers that are handed neither a decoder nor a config - `convert_sdf_voxels_to_mesh`, the sequence classes -
+    borrow it.  An engine of another GPU is never returned: a rank helper that holds engines on several devices, or a
+    test session with many decoders alive, must not have a frame built or a mesh extracted on the wrong device."""
+    if device is None:
+        import torch
+        device = torch.cuda.current_device() if torch.cuda.is_available() else None
     for ref in reversed(_LIVE):
         eng = ref()
-        if eng is not None and getattr(eng, "_h", None):
+        if eng is not None and getattr(eng, "_h", None) and (device is None or eng.device.index == device):
             return eng
     return None
+
+
+PINNED_CAP_BYTES = 256 << 20      # bound on the pinned staging an Engine keeps between calls (all threads, all classes)
 
 
 def _align(n, a=256):
@@ -119,16 +127,28 @@ class Engine:
     # -- helpers ------------------------------------------------------------------------------
     def _staging(self, nbytes):
         """Pinned host staging for one batch.  Buffers are kept per size class (powers of two) and per host thread and
-        handed out alternately from a pair that is allocated together on the first use of the class, so that no call
-        after the first pays for `cudaHostAlloc`; a batch stays valid while the next one is packed (callers that keep
-        more JointBatch objects alive at once pass cached=False)."""
+        handed out alternately from a PAIR that is allocated together on the first use of the class, so that no call
+        after the first pays for `cudaHostAlloc`; a batch stays valid while the next ONE is packed (callers that keep
+        more JointBatch objects alive at once pass cached=False).  The pairs an engine keeps are bounded by
+        PINNED_CAP_BYTES: when a new class would take the total over it, the least recently used classes are dropped
+        first (their memory goes back once the batches made from them are gone), and a class that does not fit on its
+        own is not kept at all - a one-off 1024-detection sweep no longer pins four times its blob for good."""
         import threading
         t = self.torch
         cls = 1 << max(12, int(nbytes - 1).bit_length())
         key = (threading.get_ident(), cls)
-        ring = self._pinned.get(key)
+        ring = self._pinned.pop(key, None)
         if ring is None:
-            ring = self._pinned[key] = [[t.empty(cls, dtype=t.uint8, pin_memory=True) for _ in range(2)], 0]
+            if 2 * cls > PINNED_CAP_BYTES:
+                return t.empty(cls, dtype=t.uint8, pin_memory=True)[:nbytes]
+            kept = sum(2 * k[1] for k in self._pinned)
+            for old in list(self._pinned):                       # dicts keep insertion order: oldest use first
+                if kept + 2 * cls <= PINNED_CAP_BYTES:
+                    break
+                kept -= 2 * old[1]
+                del self._pinned[old]
+            ring = [[t.empty(cls, dtype=t.uint8, pin_memory=True) for _ in range(2)], 0]
+        self._pinned[key] = ring                                 # (re-)inserted last = most recently used
         buf = ring[0][ring[1] & 1]
         ring[1] += 1
         return buf[:nbytes]

@@ -48,22 +48,40 @@ _last_engine = None
 
 def _resolve_engine(decoder=None, configs=None):
     """Engine for callers that were not handed a decoder (the sequence classes, constructed by `src/System.cc:99`
-    with `(path, cfg)` only): the decoder's own engine if given; else the engine the process already made for its
-    Optimizer; else one for `get_decoder(configs)` - cached per DeepSDF_DIR, i.e. the very module `System.cc:98`
-    created, so the Optimizer constructed later (`src/LocalMapping.cc:39`) shares it."""
+    with `(path, cfg)` only).  Resolved by what the caller names before anything is borrowed:
+      1. the decoder's own engine if a decoder is given;
+      2. with configs whose DeepSDF_DIR this process has already loaded (`get_decoder` caches the module per
+         directory - the very module `System.cc:98` created): that module's engine, so the sequence and the
+         Optimizer constructed later (`src/LocalMapping.cc:39`) share one handle whatever else is alive;
+      3. a live engine on the CURRENT CUDA device (never another GPU's): the one this module made most recently
+         there, else any engine alive on that device (`convert_sdf_voxels_to_mesh` needs no decoder at all);
+      4. with configs: a new engine for `get_decoder(configs)`."""
     if decoder is not None:
         return _engine_for(decoder)
+    from reconstruct import utils as _u
+    ddir = None
+    if configs is not None:
+        try:
+            ddir = configs["DeepSDF_DIR"] if isinstance(configs, dict) else getattr(configs, "DeepSDF_DIR", None)
+        except KeyError:
+            ddir = None
+    if ddir is not None:
+        import os
+        cached = _u._decoders.get(os.path.abspath(ddir))
+        if cached is not None:
+            return _engine_for(cached)
+    import torch
+    cur = torch.cuda.current_device() if torch.cuda.is_available() else None
     eng = _last_engine() if _last_engine is not None else None
-    if eng is not None and getattr(eng, "_h", None):
+    if eng is not None and getattr(eng, "_h", None) and (cur is None or eng.device.index == cur):
         return eng
     from dspslam.engine import last_engine
-    eng = last_engine()
+    eng = last_engine(cur)
     if eng is not None:
         return eng
-    if configs is None:
-        raise ValueError("no decoder, no configs and no live engine to borrow")
-    from reconstruct.utils import get_decoder
-    return _engine_for(get_decoder(configs))
+    if ddir is None:
+        raise ValueError("no decoder, no configs.DeepSDF_DIR and no live engine on the current CUDA device to borrow")
+    return _engine_for(_u.get_decoder(configs))
 
 
 class Optimizer(object):

@@ -59,14 +59,20 @@ enum {
 enum {
     DSPSLAM_MODE_FP32 = 0, /* FP32 FFMA validation mode (1e-5 parity)                    */
     DSPSLAM_MODE_TC = 1,   /* tcgen05 tensor cores, FP16 operands / FP32 TMEM accumulate, with the two precision
-                            * measures that keep a GN step on the FP32 reference's: ray samples next to a decision
-                            * threshold are evaluated a second time at FP32 grade (joint_params.refine_window), and the
-                            * SDF+Jacobian kernel multiplies by hi(W) + lo(W) (two MMA passes per K chunk)             */
+                            * measures that keep a GN step on the FP32 reference's.  (1) In the GN drivers, ray samples
+                            * next to a decision threshold are evaluated a second time at FP32 grade
+                            * (joint_params.refine_window).  (2) The SDF+Jacobian kernel (dspslam_sdf_jac, GN drivers)
+                            * multiplies by hi(W) + lo(W) - two MMA passes per K chunk - in the FORWARD sweep of layers
+                            * 4-7 only (DSPSLAM_Q_WSPLIT_MASK, default 0xF0); layers 0-3, layer 8 and the whole
+                            * backward (input-gradient) sweep are single FP16 passes.  The forward-only entry points
+                            * (dspslam_sdf, dspslam_mean_sdf[_noalloc], dspslam_grid_sdf) are single-pass FP16 in EVERY
+                            * tensor-core mode, this one, _FAST and _EXACT alike (SDF within 1e-3 of FP32).           */
     DSPSLAM_MODE_TC_FAST = 4, /* tcgen05, single FP16 pass everywhere (round-1 arithmetic): ~12 % faster, per-step
                                * parity with the reference 88 % instead of >= 95 % of the steps          */
-    DSPSLAM_MODE_TC_EXACT = 5 /* tcgen05 at FP32 grade where it matters: the SDF+Jacobian rows are evaluated with both
-                               * operands as hi+lo FP16 pairs in both sweeps (k_tc_jacx, 64-row tiles; ~4x the tensor
-                               * work per row), the ray samples as in DSPSLAM_MODE_TC                                  */
+    DSPSLAM_MODE_TC_EXACT = 5 /* tcgen05 at FP32 grade where it matters: the SDF+Jacobian rows (dspslam_sdf_jac, GN
+                               * drivers) are evaluated with both operands as hi+lo FP16 pairs in both sweeps
+                               * (k_tc_jacx, 64-row tiles; ~4x the tensor work per row), the ray samples as in
+                               * DSPSLAM_MODE_TC.  Forward-only entry points: single-pass FP16, see above.              */
 };
 
 /* per-object status written by the Gauss-Newton drivers */
@@ -101,6 +107,18 @@ int dspslam_abi_version(void);
  * needs (512 - code_len - 3), rounded up to 16, to be a multiple of its 32-wide K stages (code_len 64 and 32 - the
  * two lengths the reference's callers handle, src/LocalMapping_util.cc:416-426 - qualify). */
 int dspslam_mode_available(const dspslam_handle* h, int mode);
+/* Settings a handle runs with, as integers (-1 and a message for a null handle / unknown `what`).
+ * Environment variables (read ONCE, by dspslam_create; experiment knobs, not needed in production - both change what
+ * DSPSLAM_MODE_TC does for every handle created afterwards in the process, so a deployment should leave them unset
+ * and a benchmark should print dspslam_query's answers next to its numbers):
+ *   DSPSLAM_WSPLIT_MASK  integer 0..255 (any strtol base); bit k (k = 1..7) = the SDF+Jacobian kernel of
+ *                        DSPSLAM_MODE_TC multiplies by hi(W_k) + lo(W_k) in the FORWARD sweep of layer k.  Default 0xF0
+ *                        (layers 4-7).  0 gives DSPSLAM_MODE_TC the Jacobian arithmetic of DSPSLAM_MODE_TC_FAST.  Anything
+ *                        that does not parse makes dspslam_create fail with DSPSLAM_E_BADARG.
+ *   DSPSLAM_JAC_EARLY    non-zero: Jacobian tiles that hold surface rows only run on a second stream beside the ray
+ *                        pipeline (bit-identical results, measured neutral; default off). */
+enum { DSPSLAM_Q_WSPLIT_MASK = 0, DSPSLAM_Q_JAC_EARLY = 1, DSPSLAM_Q_DEVICE = 2 };
+int dspslam_query(const dspslam_handle* h, int what);
 /* number of kernels launched by this handle so far (for bench.py's gpu_launches) */
 int64_t dspslam_launch_count(const dspslam_handle* h);
 

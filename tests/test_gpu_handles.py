@@ -210,3 +210,27 @@ def test_early_jacobian_tiles_on_second_stream_bit_identical(mode):
         assert np.array_equal(a.t_cam_obj, b.t_cam_obj) and np.array_equal(a.code, b.code)
         assert np.array_equal(a.dbg, b.dbg) and np.array_equal(a.status, b.status)
     assert (a.status == 0).all()
+
+
+def test_query_reports_the_knobs_and_a_bad_mask_is_refused(monkeypatch):
+    """dspslam_query gives back what the environment variables of dspslam_create selected (include/dspslam.h); a mask
+    that does not parse fails the creation instead of silently selecting the tc_fast Jacobian arithmetic."""
+    from dspslam import _native as N
+    from dspslam import synth
+    from dspslam.engine import Engine
+    monkeypatch.delenv("DSPSLAM_WSPLIT_MASK", raising=False)
+    monkeypatch.delenv("DSPSLAM_JAC_EARLY", raising=False)
+    e = Engine(synth.load_wfit())
+    assert e.lib.dspslam_query(e._h, N.Q_WSPLIT_MASK) == 0xF0
+    assert e.lib.dspslam_query(e._h, N.Q_JAC_EARLY) == 0
+    assert e.lib.dspslam_query(e._h, N.Q_DEVICE) == e.device.index
+    assert e.lib.dspslam_query(e._h, 99) == -1 and e.lib.dspslam_query(None, 0) == -1
+    monkeypatch.setenv("DSPSLAM_WSPLIT_MASK", "0x0E")
+    monkeypatch.setenv("DSPSLAM_JAC_EARLY", "1")
+    e2 = Engine(synth.load_wfit())
+    assert e2.lib.dspslam_query(e2._h, N.Q_WSPLIT_MASK) == 0x0E and e2.lib.dspslam_query(e2._h, N.Q_JAC_EARLY) == 1
+    monkeypatch.delenv("DSPSLAM_JAC_EARLY")
+    for bad in ("oxF0", "", "300", "-1", "12junk"):
+        monkeypatch.setenv("DSPSLAM_WSPLIT_MASK", bad)
+        with pytest.raises(N.NativeError, match="DSPSLAM_WSPLIT_MASK"):
+            Engine(synth.load_wfit())

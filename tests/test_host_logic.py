@@ -94,3 +94,42 @@ def test_staging_ring_alternates_without_reallocating():
     assert calls == [8192, 8192]                       # one pair for the 8 KiB class, allocated together
     assert a.numel() == 5000 and b.numel() == 6000
     assert a.data_ptr() != b.data_ptr() and a.data_ptr() == c.data_ptr()
+
+
+def test_staging_ring_is_bounded_in_bytes(monkeypatch):
+    """The pinned pairs an engine keeps stay under PINNED_CAP_BYTES: least recently used classes go first, and a class
+    that cannot fit on its own is handed out without being kept."""
+    import torch
+    from dspslam import engine as E
+    e = E.Engine.__new__(E.Engine)
+    e.torch, e._pinned = torch, {}
+    real_empty = torch.empty
+    monkeypatch.setattr(torch, "empty", lambda n, dtype=None, pin_memory=False: real_empty(n, dtype=dtype))
+    monkeypatch.setattr(E, "PINNED_CAP_BYTES", 64 << 10)
+    e._staging(5000)                 # 8 KiB class: 16 KiB kept
+    e._staging(12000)                # 16 KiB class: 32 KiB kept (48 KiB total)
+    e._staging(5000)                 # touches the 8 KiB class: the 16 KiB class is now the oldest
+    e._staging(10000 + 8192)         # 32 KiB class = 64 KiB on its own: everything older has to go
+    assert sorted(k[1] for k in e._pinned) == [32768]
+    big = e._staging(40000)          # 64 KiB class: a pair would be 128 KiB > cap, not kept
+    assert big.numel() == 40000 and sorted(k[1] for k in e._pinned) == [32768]
+
+
+def test_last_engine_never_crosses_devices():
+    """last_engine(device) only returns an engine living on that device (fake engines: no CUDA needed)."""
+    import weakref
+    import torch
+    from dspslam import engine as E
+
+    class Fake:
+        def __init__(self, idx):
+            self._h, self.device = 1, torch.device("cuda", idx)
+    a, b = Fake(0), Fake(1)
+    saved = list(E._LIVE)
+    try:
+        E._LIVE[:] = [weakref.ref(a), weakref.ref(b)]
+        assert E.last_engine(0) is a and E.last_engine(1) is b and E.last_engine(2) is None
+        b._h = None                  # closed engines are skipped
+        assert E.last_engine(1) is None
+    finally:
+        E._LIVE[:] = saved

@@ -1,11 +1,18 @@
 """DRAM traffic per launch of the decoder kernels, from a committed `ncu --set full` capture:
-    python tools/ncu_traffic.py profiles/r02_prof_bench_k_tc.ncu-rep > profiles/r02_traffic.json
+    python tools/ncu_traffic.py gpurun_out/r03_prof_bench_k_tc.ncu-rep > profiles/r03_traffic.json
+The JSON records the hash of the kernel sources and the workload string of the tree it is made in (run it right after
+the capture, on the tree that was captured): bench.py prints `roofline.traffic` from the newest such file only when
+both still match, null otherwise.  The .ncu-rep itself stays out of git (20 MB); the text summaries are committed.
 bench.py reads the JSON for `roofline.traffic` (dram__bytes_read.sum + dram__bytes_write.sum of the largest launch of
 each kernel in the capture - the phase-0 forward launch, the Jacobian launch, the refinement launch)."""
 import csv
 import json
+import os
 import subprocess
 import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), ".."))
+import bench  # noqa: E402  (kernel_src_sha16 / workload_desc: the identity of what was captured)
 
 rep = sys.argv[1]
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv", "--metrics",
@@ -24,4 +31,5 @@ for r in rows[2:]:
     if name not in best or ms > best[name]["ms_under_ncu"]:
         best[name] = {"dram_read_bytes": int(rd), "dram_write_bytes": int(wr), "traffic_bytes": int(rd + wr),
                       "ms_under_ncu": ms}
-print(json.dumps({"source": rep, "kernels": best}, indent=1))
+print(json.dumps({"source": rep, "kernel_src_sha16": bench.kernel_src_sha16(), "workload": bench.workload_desc(),
+                  "kernels": best}, indent=1))

@@ -9,6 +9,10 @@ oracle/make_goldens*.py) - the numbers behind north_star's ">= 95 % of reference
                tolerance when |dt| < 1 cm, rotation < 0.1 deg and |dcode| / max(|code|, 0.1) < 1e-2
                (also bulk_c3.npz: 32 mono detections x 20 iterations; bulk_c2.npz: the 16 detections of the
                benchmarked C2 batch itself, M = 2048 / N = 2248, x 10 iterations)
+  free run     bulk_c1.npz / bulk_c1_heldout.npz: all 10 iterations free-running from the reference's initial state, END
+               state against the reference's end state (north_star's wording); the FP32 mode is the floor
+  held-out     bulk_c1_heldout.npz: 128 further cars (seeds 1000..1127) that played no part in choosing the default
+               hi/lo layer mask - the population the tests assert on
   objects      fraction of objects whose LAST step (the state the caller receives) is within tolerance, and
                fraction with every one of the 10 steps within tolerance
 
@@ -55,8 +59,9 @@ def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
     make = synth.make_mono_detection if mono else synth.make_kitti_detection
     if "c2" in which:                  # the benchmarked batch itself: M = 2048 surface points, 2248 rays
         make = lambda k: synth.make_kitti_detection(k, M=2048, n_bg=200)
+    k0 = int(b["k0"]) if "k0" in b else 0         # held-out populations start at another seed (make_goldens_heldout.py)
     ks = [k for k in range(min(n_objects, b["T_oc"].shape[0])) if b["is_good"][k]]
-    dets = [make(k) for k in ks]
+    dets = [make(k0 + k) for k in ks]
     for k, d in zip(ks, dets):      # the generator must still produce the inputs the reference ran on
         chk = float(sum(np.asarray(d[n], np.float64).sum() for n in ("t_cam_obj", "pts", "rays", "depth")))
         assert abs(chk - float(b["in_sum"][k])) < 1e-6 * max(1.0, abs(chk)), "synthetic generator drifted (object %d)" % k
@@ -92,12 +97,55 @@ def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
             "tolerance": "1 cm / 0.1 deg / 1e-2 per teacher-forced GN step", "golden": which}
 
 
+def free_run_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
+    """north_star's end-state criterion as it is worded: ALL iterations free-running from the reference's initial
+    state (no teacher forcing), the state the caller receives against the reference's own end state
+    (`optimizer.py:120-205` -> `src/LocalMapping_util.cc:181-194`); within = 1 cm, 0.1 deg, |dcode| / max(|code|, 0.1)
+    < 1e-2.  The reference is chaotic against ITSELF over 10 iterations (tests/golden/noise_floor.json), so the FP32
+    validation mode of this library - 1e-5 per query - is reported next to the tensor-core modes as the floor."""
+    from dspslam import synth
+    b = _load(which)
+    cfg = synth.kitti_config()
+    k0 = int(b["k0"]) if "k0" in b else 0
+    ks = [k for k in range(min(n_objects, b["T_oc"].shape[0])) if b["is_good"][k]]
+    n_it = b["T_oc"].shape[1]
+    prm = joint_params(cfg, n_it)
+    batch = []
+    for k in ks:
+        d = synth.make_kitti_detection(k0 + k)
+        T_co = np.linalg.inv(b["T_oc"][k, 0].astype(np.float64)).astype(np.float32)
+        batch.append((T_co, d["pts"], d["rays"], d["depth"], b["code_it"][k, 0]))
+    res = eng.gn_joint(batch, prm, mode=mode.split(":")[0])
+    E = np.zeros((len(ks), 3))
+    for i, k in enumerate(ks):
+        if res.status[i] != 0:
+            E[i] = (1.0, 90.0, 1.0)
+            continue
+        dt, ang, _ = synth.pose_errors(res.t_cam_obj[i], b["t_cam_obj"][k])
+        cn = b["code"][k]
+        E[i] = (dt, ang, np.linalg.norm(res.code[i] - cn) / max(np.linalg.norm(cn), 0.1))
+    ok = (E[:, 0] < 1e-2) & (E[:, 1] < 0.1) & (E[:, 2] < 1e-2)
+    loose = (E[:, 0] < 5e-2) & (E[:, 1] < 1.0) & (E[:, 2] < 1e-1)
+    q = lambda a, p: float(np.quantile(a, p))
+    return {"objects": len(ks), "iterations": int(n_it), "within": float(ok.mean()), "within_5cm_1deg_1e-1": float(loose.mean()),
+            "dt_m": {"median": q(E[:, 0], .5), "q95": q(E[:, 0], .95)},
+            "rot_deg": {"median": q(E[:, 1], .5), "q95": q(E[:, 1], .95)},
+            "code_rel": {"median": q(E[:, 2], .5), "q95": q(E[:, 2], .95)},
+            "tolerance": "1 cm / 0.1 deg / 1e-2 on the END state, free-running", "golden": which}
+
+
 def parity(eng, mode, n_objects=128):
     out = {"mode": mode}
     if not str(mode).startswith("mix"):
         out["jacobian"] = jacobian_stats(eng, mode)
     if os.path.isfile(os.path.join(GOLD, "bulk_c1.npz")):
         out["c1"] = step_stats(eng, mode, n_objects)
+        if not str(mode).startswith("mix"):
+            out["c1_free_run"] = free_run_stats(eng, mode, n_objects)
+    if os.path.isfile(os.path.join(GOLD, "bulk_c1_heldout.npz")):
+        out["c1_heldout"] = step_stats(eng, mode, n_objects, "bulk_c1_heldout.npz")
+        if not str(mode).startswith("mix"):
+            out["c1_heldout_free_run"] = free_run_stats(eng, mode, n_objects, "bulk_c1_heldout.npz")
     if os.path.isfile(os.path.join(GOLD, "bulk_c3.npz")):
         out["c3"] = step_stats(eng, mode, 32, "bulk_c3.npz")
     if os.path.isfile(os.path.join(GOLD, "bulk_c2.npz")):
