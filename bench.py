@@ -449,6 +449,11 @@ def ours_arm(args, rank, world, local_rank):
                           "heldout_last": frac("c1_heldout", "objects_last_step_within"),
                           "heldout_free_run": frac("c1_heldout_free_run", "within"),
                           "c2_steps": frac("c2", "steps_within"), "c3_steps": frac("c3", "steps_within")}
+        try:
+            with open(os.path.join(ROOT, "tests", "golden", "noise_floor_bulk.json")) as f:
+                tail["parity"]["reference_vs_itself_free_run"] = r3(json.load(f)["summary"]["within"])
+        except (OSError, KeyError, ValueError):
+            pass
     line["tail"] = tail
     print(json.dumps(line), flush=True)
     if world > 1:

@@ -71,8 +71,9 @@ enum {
                                * parity with the reference 88 % instead of >= 95 % of the steps          */
     DSPSLAM_MODE_TC_EXACT = 5 /* tcgen05 at FP32 grade where it matters: the SDF+Jacobian rows (dspslam_sdf_jac, GN
                                * drivers) are evaluated with both operands as hi+lo FP16 pairs in both sweeps
-                               * (k_tc_jacx, 64-row tiles; ~4x the tensor work per row), the ray samples as in
-                               * DSPSLAM_MODE_TC.  Forward-only entry points: single-pass FP16, see above.              */
+                               * (k_tc_jacx, 64-row tiles; ~4x the tensor work per row), and every ray sample inside
+                               * the occupancy band is evaluated a second time at FP32 grade (refine_window default 1.0
+                               * instead of 0.05).  Forward-only entry points: single-pass FP16, see above.              */
 };
 
 /* per-object status written by the Gauss-Newton drivers */
@@ -188,7 +189,9 @@ typedef struct {
                                 * clamp and with_grad mask, loss.py:98-102).  A ray sample the FP16-operand forward pass
                                 * leaves within refine_window * cut_off of such a threshold is evaluated a second time
                                 * with hi+lo FP16 operand pairs (FP32-grade) before the per-ray scan, so the selected row
-                                * set follows the FP32 reference.  0 = library default (0.05); < 0 switches it off. */
+                                * set follows the FP32 reference.  0 = library default: 0.05 in DSPSLAM_MODE_TC (the decisions
+                                * only), 1.0 in DSPSLAM_MODE_TC_EXACT (every sample inside the occupancy band, so that the
+                                * VALUES entering the residuals are FP32-grade too); < 0 switches it off. */
 } dspslam_joint_params;
 
 /* A batch of B independent detections, concatenated.

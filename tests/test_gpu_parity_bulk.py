@@ -11,6 +11,13 @@ relative code; and the per-entry Jacobian error against `get_batch_sdf_jacobian`
             thresholds + hi/lo weights in the SDF+Jacobian kernel): >= 95 % of the steps, >= 95 % of the objects
             (last step), >= 95 % of the Jacobian rows with every entry within 1e-3
   tc_fast   single FP16 pass everywhere (round-1 arithmetic): reported, only held to a floor
+
+Two further populations (round 3):
+  held-out  bulk_c1_heldout.npz: 128 cars with other seeds (oracle/make_goldens_heldout.py) that played no part in
+            choosing the default hi/lo layer mask - the >= 95 % statement is asserted on them as well
+  free run  north_star's end-state sentence as worded: all 10 iterations free-running, END state against the
+            reference's.  The reference does not meet it against ITSELF (tests/golden/noise_floor_bulk.json: surface
+            points moved by one FP32 ulp -> 51 % of 128 objects within tolerance), so the yardstick is that floor.
 """
 import os
 import sys
@@ -115,3 +122,42 @@ def test_jacobian_outlier_rows_are_relu_kink_rows(eng):
     assert np.all(near_kink[bad]), "a Jacobian row off by more than 1e-3 without a ReLU unit at its kink"
     assert err[~near_kink].max() <= 1e-3 if (~near_kink).any() else True
     assert err.max() < 0.2
+
+
+def _floor():
+    import json
+    with open(os.path.join(ROOT, "tests", "golden", "noise_floor_bulk.json")) as f:
+        return json.load(f)["summary"]
+
+
+def test_held_out_population(stats):
+    """The teacher-forced statistic on 128 detections that were NOT used to pick the default hi/lo layer mask
+    (api.cu: wsplit_mask).  Measured: fp32 0.999 / 1.0, tc 0.9555 of 1 280 steps / 0.961 of the objects (last step),
+    tc_exact 0.991 / 0.977.  Binomial standard error at n = 1 280 is 0.6 points: the default mode meets the 95 %
+    statement on fresh data with no margin to spare, and the docs say so."""
+    f, t, x = stats("fp32")["c1_heldout"], stats("tc")["c1_heldout"], stats("tc_exact")["c1_heldout"]
+    assert f["objects"] == t["objects"] == 128
+    assert f["steps_within"] >= 0.99 and f["objects_last_step_within"] >= 0.99
+    assert t["steps_within"] >= 0.95 and t["objects_last_step_within"] >= 0.95, t
+    assert x["steps_within"] >= 0.985 and x["objects_last_step_within"] >= 0.97, x
+
+
+def test_free_run_end_state_against_the_reference_floor(stats):
+    """Free-running end state (north_star's wording) of every shipped mode next to the reference's own
+    reproducibility.  Fractions of 128 objects within 1 cm / 0.1 deg / 1e-2, bulk_c1 | held-out:
+        reference vs itself (+1 ulp)   0.51
+        fp32                           0.59 | 0.51      at the floor
+        tc_exact (window 1.0)          0.47 | 0.38      within ~1-3 binomial sigma (4.4 points) of the floor
+        tc (benchmarked default)       0.16 | 0.06      KNOWN GAP: FP16 Jacobian operands, see DESIGN.md section 5
+    Asserted: the FP32 mode reaches the floor minus 5 points; the exact mode stays within 15 points of it and well
+    above the default; the default mode is only guarded against getting worse (loose criterion 5 cm / 1 deg / 0.1)."""
+    floor = _floor()
+    assert floor["objects"] == 128 and 0.3 < floor["within"] < 0.8
+    for key in ("c1_free_run", "c1_heldout_free_run"):
+        f, x, t = stats("fp32")[key], stats("tc_exact")[key], stats("tc")[key]
+        assert f["within"] >= floor["within"] - 0.05, (key, f)
+        assert f["within_5cm_1deg_1e-1"] >= 0.90, (key, f)
+        assert x["within"] >= floor["within"] - 0.15, (key, x)
+        assert x["within"] >= t["within"] + 0.15, (key, x, t)
+        assert x["within_5cm_1deg_1e-1"] >= 0.85, (key, x)
+        assert t["within_5cm_1deg_1e-1"] >= 0.65 and t["dt_m"]["median"] < 3e-3 and t["rot_deg"]["median"] < 0.2, (key, t)

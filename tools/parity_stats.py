@@ -40,6 +40,16 @@ def joint_params(cfg, iters):
                 num_depth_samples=cfg.optimizer.num_depth_samples)
 
 
+def _window(prm, mode):
+    """mode suffixes: ':norefine' = tensor-core forward pass without the FP32-grade second evaluation;
+    ':w<x>' = joint_params.refine_window = x (e.g. 'tc:w1.0': every sample inside the occupancy band twice)."""
+    for part in str(mode).split(":")[1:]:
+        if part == "norefine":
+            prm["refine_window"] = -1.0
+        elif part.startswith("w"):
+            prm["refine_window"] = float(part[1:])
+
+
 def jacobian_stats(eng, mode):
     mode = mode.split(":")[0]
     g = _load("queries_wfit.npz")
@@ -67,8 +77,7 @@ def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
         assert abs(chk - float(b["in_sum"][k])) < 1e-6 * max(1.0, abs(chk)), "synthetic generator drifted (object %d)" % k
     n_it = b["T_oc"].shape[1]
     prm = joint_params(cfg, 1)
-    if mode.endswith(":norefine"):          # tensor-core forward pass without the FP32-grade second evaluation
-        prm["refine_window"] = -1.0
+    _window(prm, mode)
     mode = mode.split(":")[0]
     E = np.zeros((len(ks), n_it, 3))
     for e in range(n_it):
@@ -110,6 +119,7 @@ def free_run_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
     ks = [k for k in range(min(n_objects, b["T_oc"].shape[0])) if b["is_good"][k]]
     n_it = b["T_oc"].shape[1]
     prm = joint_params(cfg, n_it)
+    _window(prm, mode)
     batch = []
     for k in ks:
         d = synth.make_kitti_detection(k0 + k)
