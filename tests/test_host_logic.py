@@ -133,3 +133,16 @@ def test_last_engine_never_crosses_devices():
         assert E.last_engine(1) is None
     finally:
         E._LIVE[:] = saved
+
+
+def test_wilson_interval_of_the_parity_fractions():
+    """tools/parity_stats.py reports a 95 % interval next to each population fraction (the margins over 95 %
+    are thin, so say how thin).  Known answers: 1 223 of 1 280 -> about [0.943, 0.966]."""
+    import sys as _s
+    _s.path.insert(0, os.path.join(ROOT, "tools"))
+    import parity_stats
+    lo, hi = parity_stats.wilson(1223, 1280)
+    assert abs(lo - 0.9427) < 2e-3 and abs(hi - 0.9655) < 2e-3
+    lo, hi = parity_stats.wilson(128, 128)
+    assert hi == pytest.approx(1.0) and 0.96 < lo < 0.98
+    assert parity_stats.wilson(0, 0) == [0.0, 1.0]

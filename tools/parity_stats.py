@@ -50,6 +50,17 @@ def _window(prm, mode):
             prm["refine_window"] = float(part[1:])
 
 
+def wilson(k, n, z=1.96):
+    """95 % Wilson score interval of a fraction k / n (the populations here are a few hundred to a thousand trials)."""
+    if n == 0:
+        return [0.0, 1.0]
+    p = k / n
+    d = 1 + z * z / n
+    c = (p + z * z / (2 * n)) / d
+    h = z * np.sqrt(p * (1 - p) / n + z * z / (4 * n * n)) / d
+    return [float(c - h), float(c + h)]
+
+
 def jacobian_stats(eng, mode):
     mode = mode.split(":")[0]
     g = _load("queries_wfit.npz")
@@ -99,6 +110,8 @@ def step_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
     ok = (E[..., 0] < 1e-2) & (E[..., 1] < 0.1) & (E[..., 2] < 1e-2)
     q = lambda a, p: float(np.quantile(a, p))
     return {"objects": len(ks), "steps": int(ok.size), "steps_within": float(ok.mean()),
+            "steps_within_ci95": wilson(int(ok.sum()), int(ok.size)),
+            "objects_last_step_within_ci95": wilson(int(ok[:, -1].sum()), int(ok.shape[0])),
             "objects_last_step_within": float(ok[:, -1].mean()), "objects_all_steps_within": float(ok.all(axis=1).mean()),
             "dt_m": {"median": q(E[..., 0], .5), "q95": q(E[..., 0], .95), "max": float(E[..., 0].max())},
             "rot_deg": {"median": q(E[..., 1], .5), "q95": q(E[..., 1], .95), "max": float(E[..., 1].max())},
@@ -137,7 +150,8 @@ def free_run_stats(eng, mode, n_objects=128, which="bulk_c1.npz"):
     ok = (E[:, 0] < 1e-2) & (E[:, 1] < 0.1) & (E[:, 2] < 1e-2)
     loose = (E[:, 0] < 5e-2) & (E[:, 1] < 1.0) & (E[:, 2] < 1e-1)
     q = lambda a, p: float(np.quantile(a, p))
-    return {"objects": len(ks), "iterations": int(n_it), "within": float(ok.mean()), "within_5cm_1deg_1e-1": float(loose.mean()),
+    return {"objects": len(ks), "iterations": int(n_it), "within": float(ok.mean()),
+            "within_ci95": wilson(int(ok.sum()), int(ok.size)), "within_5cm_1deg_1e-1": float(loose.mean()),
             "dt_m": {"median": q(E[:, 0], .5), "q95": q(E[:, 0], .95)},
             "rot_deg": {"median": q(E[:, 1], .5), "q95": q(E[:, 1], .95)},
             "code_rel": {"median": q(E[:, 2], .5), "q95": q(E[:, 2], .95)},
