@@ -449,6 +449,11 @@ def ours_arm(args, rank, world, local_rank):
                           "heldout_last": frac("c1_heldout", "objects_last_step_within"),
                           "heldout_free_run": frac("c1_heldout_free_run", "within"),
                           "c2_steps": frac("c2", "steps_within"), "c3_steps": frac("c3", "steps_within")}
+        for m, v in (par.get("free_run_other_modes") or {}).items():
+            if not isinstance(v, dict):
+                continue
+            tail["parity"][m + "_free_run"] = r3(v.get("c1"))
+            tail["parity"][m + "_heldout_free_run"] = r3(v.get("heldout"))
         try:
             with open(os.path.join(ROOT, "tests", "golden", "noise_floor_bulk.json")) as f:
                 tail["parity"]["reference_vs_itself_free_run"] = r3(json.load(f)["summary"]["within"])
@@ -585,6 +590,16 @@ def other_configs(args, rank, world, local_rank, dec, opt, barrier, max_over_ran
         import parity_stats
         try:
             out["parity"] = parity_stats.parity(eng, args.mode)
+            # the free-running end state of the two modes that reach the reference's own reproducibility floor, for
+            # comparison with the benchmarked mode's
+            try:
+                out["parity"]["free_run_other_modes"] = {
+                    m: {k: parity_stats.free_run_stats(eng, m, 128, w)["within"]
+                        for k, w in (("c1", "bulk_c1.npz"), ("heldout", "bulk_c1_heldout.npz"))
+                        if os.path.isfile(os.path.join(parity_stats.GOLD, w))}
+                    for m in ("fp32", "tc_exact") if m != args.mode}
+            except Exception as ex:  # noqa: BLE001
+                out["parity"]["free_run_other_modes"] = {"error": str(ex)[-200:]}
         except Exception as ex:  # noqa: BLE001
             out["parity"] = {"error": str(ex)[-300:]}
     barrier()
